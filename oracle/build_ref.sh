@@ -1,0 +1,51 @@
+#!/usr/bin/env bash
+# TEST INFRASTRUCTURE.  Builds (1) oracle/_ref/liboracle.so, the plain-C restatement, and
+# (2) when /root/reference is present, oracle/_ref/libphmm_ref.so: the reference's own
+# pair-HMM sources compiled IN PLACE (nothing is copied) plus oracle/ref_harness.cpp.
+# The reference's own build (gradle + cmake) cannot run here: its CMakeLists.txt files were
+# never committed (root .gitignore ignores *.txt) and there is no JDK; see SURVEY.md 8c.
+#   canonical oracle     : -ffp-contract=off  (AVX-256 and AVX-512 TUs bit-identical)
+#   libphmm_ref_fma.so   : g++ defaults (the AVX-512 TU gets contracted vfmadd) -- tolerance check only
+set -euo pipefail
+HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
+OUT="$HERE/_ref"
+REF="${PHMM_REFERENCE_ROOT:-/root/reference}"
+P="$REF/tools/GKL/src/main/native"
+mkdir -p "$OUT"
+
+gcc -O2 -std=c11 -fPIC -shared -fopenmp -ffp-contract=off \
+    -o "$OUT/liboracle.so" "$HERE/phmm_oracle.c" -lm
+echo "built $OUT/liboracle.so"
+
+if [ ! -d "$P/pairhmm" ]; then
+  echo "reference sources not found at $P -- keeping any prebuilt $OUT/libphmm_ref.so"
+  exit 0
+fi
+
+# IntelPairHmmCSource.cpp:7 includes IntelPairHmm.h -> <jni.h>; there is no JDK here.
+mkdir -p "$OUT/stub"
+cat > "$OUT/stub/jni.h" <<'EOS'
+#ifndef PHMM_STUB_JNI_H
+#define PHMM_STUB_JNI_H
+#define JNIEXPORT
+#define JNICALL
+typedef void JNIEnv; typedef void* jclass; typedef void* jobject; typedef void* jobjectArray;
+typedef void* jdoubleArray; typedef unsigned char jboolean; typedef int jint;
+#endif
+EOS
+
+build_variant () {   # $1 = output name, $2 = extra flags
+  local name="$1" extra="$2" obj="$OUT/obj_$1"
+  mkdir -p "$obj"
+  local CXXF="-O2 -std=c++11 -fPIC -fopenmp $extra -I$OUT/stub -I$P/common -I$P/pairhmm"
+  g++ $CXXF -mavx -c "$P/pairhmm/avx_impl.cc" -o "$obj/avx_impl.o"
+  g++ $CXXF -mavx -mavx2 -mavx512f -mavx512dq -mavx512vl -c "$P/pairhmm/avx512_impl.cc" -o "$obj/avx512_impl.o"
+  g++ $CXXF -c "$P/pairhmm/pairhmm_common.cc" -o "$obj/pairhmm_common.o"
+  g++ $CXXF -c "$P/pairhmm/IntelPairHmmCSource.cpp" -o "$obj/IntelPairHmmCSource.o"
+  g++ $CXXF -c "$HERE/ref_harness.cpp" -o "$obj/ref_harness.o"
+  g++ -shared -fopenmp -Wl,-Bsymbolic -o "$OUT/$name" "$obj"/*.o -lm
+  rm -rf "$obj"
+  echo "built $OUT/$name"
+}
+build_variant libphmm_ref.so "-ffp-contract=off"
+build_variant libphmm_ref_fma.so ""
