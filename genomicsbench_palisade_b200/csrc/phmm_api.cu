@@ -1,0 +1,750 @@
+// C ABI of libphmm_cuda: context, device-resident workloads, host-buffer entry points.
+// See include/phmm_cuda.h for the contract and the reference interfaces each entry replaces.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "phmm_host.h"
+
+using namespace phmm;
+
+namespace {
+thread_local std::string g_create_error;
+}
+
+struct phmm_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    // device tables
+    float *d_ph2pr_f = nullptr, *d_mm_f = nullptr;
+    double *d_ph2pr_d = nullptr, *d_mm_d = nullptr;
+    float *d_bench = nullptr;
+    // options
+    int precision = 0, fp32_fast = 0, fp64_fast = 0, seg_cols = 0, packed = 1;
+    int force_kh = 0, force_lanes = 0;
+    std::string error;
+    std::mutex mu;     // the legacy symbols may be entered from several OpenMP threads
+};
+
+struct ClassDev {
+    KClass kc;
+    int64_t task_off = 0;     // into d_tasks
+    int32_t ntasks = 0;
+};
+
+struct phmm_workload {
+    phmm_ctx *ctx = nullptr;
+    Plan plan;                // tasks/stream vectors are released after upload
+    std::vector<ClassDev> classes;
+    int64_t n_pairs = 0, n_cells = 0, h2d_bytes = 0;
+    int64_t resc_total = 0;
+    int32_t resc_off[MAX_KH_SCALAR + 1];
+    int32_t resc_cap[MAX_KH_SCALAR + 1];
+    int precision = 0;
+    // device buffers
+    uint8_t *d_pool = nullptr;        // 5 read pools back to back
+    int64_t pool_stride = 0;
+    uint8_t *d_stream = nullptr;
+    int32_t *d_hap_len = nullptr;
+    ReadRec *d_reads = nullptr;
+    Task *d_tasks = nullptr;
+    Task *d_resc = nullptr, *d_guard = nullptr;
+    int32_t *d_ints = nullptr;        // [0..63] queue heads, [64..] ntasks per class, resc/guard counts
+    double *d_out = nullptr, *d_raw64 = nullptr;
+    float *d_raw32 = nullptr;
+    uint8_t *d_rescued = nullptr;
+    int64_t last_rescued = 0, last_rescued_cells = 0, last_guard = 0;
+};
+
+namespace {
+
+// layout of phmm_workload::d_ints
+const int INTS_COUNTER = 0;                       // one queue head per launch, up to 64 launches
+const int INTS_NTASKS = 64;                       // per FP32 class
+const int INTS_RESC = 128;                        // [MAX_KH_SCALAR + 1]
+const int INTS_GUARD = 128 + 16;
+const int INTS_TOTAL = 192;
+
+#define CUDA_TRY(ctx, expr)                                                                   \
+    do {                                                                                      \
+        cudaError_t e__ = (expr);                                                             \
+        if (e__ != cudaSuccess) {                                                             \
+            (ctx)->error = std::string(#expr) + ": " + cudaGetErrorString(e__);               \
+            return PHMM_ERR_CUDA;                                                             \
+        }                                                                                     \
+    } while (0)
+
+template <typename T>
+int dev_alloc(phmm_ctx *ctx, T **p, size_t n)
+{
+    *p = nullptr;
+    if (n == 0) n = 1;
+    cudaError_t e = cudaMalloc((void **)p, n * sizeof(T));
+    if (e != cudaSuccess) {
+        ctx->error = std::string("cudaMalloc: ") + cudaGetErrorString(e);
+        return e == cudaErrorMemoryAllocation ? PHMM_ERR_NOMEM : PHMM_ERR_CUDA;
+    }
+    return PHMM_OK;
+}
+
+}  // namespace
+
+namespace phmm {
+KernelF32 lookup_f32(const KClass &kc, bool fast)
+{
+    if (kc.vl == 1) return kc.lanes == 32 ? (fast ? lookup_f32s_f1(kc.kh) : lookup_f32s_f0(kc.kh)) : nullptr;
+    switch (kc.lanes) {
+    case 32: return fast ? lookup_f32p_l32_f1(kc.kh) : lookup_f32p_l32_f0(kc.kh);
+    case 16: return fast ? lookup_f32p_l16_f1(kc.kh) : lookup_f32p_l16_f0(kc.kh);
+    case 8:  return fast ? lookup_f32p_l8_f1(kc.kh) : lookup_f32p_l8_f0(kc.kh);
+    default: return nullptr;
+    }
+}
+KernelF64 lookup_f64(int kh, bool fast) { return fast ? lookup_f64_f1(kh) : lookup_f64_f0(kh); }
+}  // namespace phmm
+
+// ============================================================================================
+// lifetime
+// ============================================================================================
+extern "C" int phmm_abi_version(void) { return PHMM_ABI_VERSION; }
+
+extern "C" int phmm_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+extern "C" const char *phmm_last_error(const phmm_ctx *ctx)
+{
+    return ctx ? ctx->error.c_str() : g_create_error.c_str();
+}
+
+extern "C" int phmm_create(int device, phmm_ctx **out)
+{
+    if (!out) return PHMM_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        g_create_error = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                         " (libphmm_cuda has no CPU fallback)";
+        return PHMM_ERR_CUDA;
+    }
+    if (device < 0 || device >= n) { g_create_error = "device index out of range"; return PHMM_ERR_ARG; }
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) {
+        g_create_error = std::string("cudaGetDeviceProperties: ") + cudaGetErrorString(e);
+        return PHMM_ERR_CUDA;
+    }
+    if (prop.major != 10) {
+        char buf[160];
+        snprintf(buf, sizeof buf, "device %d is sm_%d%d; libphmm_cuda is built for sm_100a (B200) only", device,
+                 prop.major, prop.minor);
+        g_create_error = buf;
+        return PHMM_ERR_CUDA;
+    }
+    phmm_ctx *ctx = new phmm_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    if (const char *s = getenv("PHMM_FORCE_CLASS")) sscanf(s, "%d,%d", &ctx->force_kh, &ctx->force_lanes);
+    auto bail = [&](const char *what, cudaError_t err) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
+        phmm_destroy(ctx);
+        return PHMM_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    for (int k = 0; k < 4; ++k)
+        if ((e = cudaEventCreate(&ctx->ev[k])) != cudaSuccess) return bail("cudaEventCreate", e);
+    const HostTables &t = host_tables();
+    if ((e = cudaMalloc(&ctx->d_ph2pr_f, 128 * sizeof(float))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc(&ctx->d_ph2pr_d, 128 * sizeof(double))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc(&ctx->d_mm_f, MM_REACHABLE * sizeof(float))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc(&ctx->d_mm_d, MM_REACHABLE * sizeof(double))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc(&ctx->d_bench, 1 << 20)) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMemcpy(ctx->d_ph2pr_f, t.ph2pr_f, 128 * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy", e);
+    if ((e = cudaMemcpy(ctx->d_ph2pr_d, t.ph2pr_d, 128 * sizeof(double), cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy", e);
+    if ((e = cudaMemcpy(ctx->d_mm_f, t.mm_f.data(), MM_REACHABLE * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy", e);
+    if ((e = cudaMemcpy(ctx->d_mm_d, t.mm_d.data(), MM_REACHABLE * sizeof(double), cudaMemcpyHostToDevice)) != cudaSuccess) return bail("cudaMemcpy", e);
+    *out = ctx;
+    return PHMM_OK;
+}
+
+extern "C" int phmm_destroy(phmm_ctx *ctx)
+{
+    if (!ctx) return PHMM_OK;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->d_ph2pr_f); cudaFree(ctx->d_ph2pr_d); cudaFree(ctx->d_mm_f); cudaFree(ctx->d_mm_d);
+    cudaFree(ctx->d_bench);
+    for (int k = 0; k < 4; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return PHMM_OK;
+}
+
+extern "C" int phmm_set_option(phmm_ctx *ctx, int option, int64_t value)
+{
+    if (!ctx) return PHMM_ERR_ARG;
+    switch (option) {
+    case PHMM_OPT_PRECISION:   if (value < 0 || value > 2) break; ctx->precision = (int)value; return PHMM_OK;
+    case PHMM_OPT_FP32_KERNEL: if (value < 0 || value > 1) break; ctx->fp32_fast = (int)value; return PHMM_OK;
+    case PHMM_OPT_FP64_KERNEL: if (value < 0 || value > 1) break; ctx->fp64_fast = (int)value; return PHMM_OK;
+    case PHMM_OPT_SEG_COLS:    if (value < 0 || value > (1 << 24)) break; ctx->seg_cols = (int)value; return PHMM_OK;
+    case PHMM_OPT_PACKED:      if (value < 0 || value > 1) break; ctx->packed = (int)value; return PHMM_OK;
+    case PHMM_OPT_FORCE_CLASS: ctx->force_kh = (int)(value >> 8); ctx->force_lanes = (int)(value & 255); return PHMM_OK;
+    default: break;
+    }
+    ctx->error = "phmm_set_option: unknown option or value out of range";
+    return PHMM_ERR_ARG;
+}
+
+extern "C" int64_t phmm_get_option(const phmm_ctx *ctx, int option)
+{
+    if (!ctx) return -1;
+    switch (option) {
+    case PHMM_OPT_PRECISION: return ctx->precision;
+    case PHMM_OPT_FP32_KERNEL: return ctx->fp32_fast;
+    case PHMM_OPT_FP64_KERNEL: return ctx->fp64_fast;
+    case PHMM_OPT_SEG_COLS: return ctx->seg_cols;
+    case PHMM_OPT_PACKED: return ctx->packed;
+    case PHMM_OPT_FORCE_CLASS: return ((int64_t)ctx->force_kh << 8) | ctx->force_lanes;
+    default: return -1;
+    }
+}
+
+extern "C" int phmm_get_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d, float *consts_f,
+                               double *consts_d)
+{
+    const HostTables &t = host_tables();
+    if (ph2pr_f) memcpy(ph2pr_f, t.ph2pr_f, sizeof t.ph2pr_f);
+    if (ph2pr_d) memcpy(ph2pr_d, t.ph2pr_d, sizeof t.ph2pr_d);
+    if (mm_f) memcpy(mm_f, t.mm_f.data(), MM_REACHABLE * sizeof(float));
+    if (mm_d) memcpy(mm_d, t.mm_d.data(), MM_REACHABLE * sizeof(double));
+    if (consts_f) { consts_f[0] = t.init_f; consts_f[1] = t.log10_init_f; }
+    if (consts_d) { consts_d[0] = t.init_d; consts_d[1] = t.log10_init_d; }
+    return MM_REACHABLE;
+}
+
+// ============================================================================================
+// device-resident workloads
+// ============================================================================================
+static PlanOptions plan_options(const phmm_ctx *ctx)
+{
+    PlanOptions o;
+    o.precision = ctx->precision;
+    o.packed = ctx->packed;
+    o.seg_cols = ctx->seg_cols;
+    o.force_kh = ctx->force_kh;
+    o.force_lanes = ctx->force_lanes;
+    o.resident_warps = ctx->sm_count * 16;
+    return o;
+}
+
+extern "C" int phmm_workload_destroy(phmm_workload *w)
+{
+    if (!w) return PHMM_OK;
+    if (w->ctx) cudaSetDevice(w->ctx->device);
+    cudaFree(w->d_pool); cudaFree(w->d_stream); cudaFree(w->d_hap_len); cudaFree(w->d_reads);
+    cudaFree(w->d_tasks); cudaFree(w->d_resc); cudaFree(w->d_guard); cudaFree(w->d_ints);
+    cudaFree(w->d_out); cudaFree(w->d_raw64); cudaFree(w->d_raw32); cudaFree(w->d_rescued);
+    delete w;
+    return PHMM_OK;
+}
+
+extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, phmm_workload **out)
+{
+    if (!ctx || !fb || !out) return PHMM_ERR_ARG;
+    *out = nullptr;
+    phmm_workload *w = new phmm_workload();
+    w->ctx = ctx;
+    w->precision = ctx->precision;
+    std::string err;
+    int rc = build_plan(*fb, plan_options(ctx), &w->plan, &err);
+    if (rc != PHMM_OK) { ctx->error = err; delete w; return rc; }
+    Plan &P = w->plan;
+    w->n_pairs = P.n_pairs;
+    w->n_cells = P.n_cells;
+    if (P.classes.size() > 60) { ctx->error = "too many kernel classes"; delete w; return PHMM_ERR_ARG; }
+
+    auto fail = [&](int code) { phmm_workload_destroy(w); return code; };
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->error = "cudaSetDevice failed"; return fail(PHMM_ERR_CUDA); }
+
+    // rescue / guard lists: one per scalar class, sized for every pair of that class
+    int64_t tot = 0;
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) {
+        if (tot + P.resc_cap[k] > INT32_MAX) { ctx->error = "workload too large for one device (rescue list)"; return fail(PHMM_ERR_ARG); }
+        w->resc_off[k] = (int32_t)tot;
+        w->resc_cap[k] = (int32_t)P.resc_cap[k];
+        tot += P.resc_cap[k];
+    }
+    w->resc_total = tot;
+    const bool need_resc = (w->precision == 0);
+
+    const int64_t pool_len = P.pool_hi - P.pool_lo;
+    w->pool_stride = (pool_len + 255) & ~(int64_t)255;
+    int64_t ntasks = 0;
+    for (auto &cp : P.classes) {
+        ClassDev cd;
+        cd.kc = cp.kc;
+        cd.task_off = ntasks;
+        cd.ntasks = (int32_t)cp.tasks.size();
+        ntasks += (int64_t)cp.tasks.size();
+        w->classes.push_back(cd);
+    }
+#define WL_ALLOC(ptr, n)                                             \
+    do { int rc__ = dev_alloc(ctx, &(ptr), (size_t)(n)); if (rc__ != PHMM_OK) return fail(rc__); } while (0)
+    WL_ALLOC(w->d_pool, 5 * w->pool_stride);
+    WL_ALLOC(w->d_stream, P.stream.size());
+    WL_ALLOC(w->d_hap_len, P.hap_len.size());
+    WL_ALLOC(w->d_reads, P.reads.size());
+    WL_ALLOC(w->d_tasks, ntasks);
+    WL_ALLOC(w->d_ints, INTS_TOTAL);
+    WL_ALLOC(w->d_out, P.n_pairs);
+    WL_ALLOC(w->d_raw32, P.n_pairs);
+    WL_ALLOC(w->d_raw64, P.n_pairs);
+    WL_ALLOC(w->d_rescued, P.n_pairs);
+    if (need_resc) {
+        WL_ALLOC(w->d_resc, tot);
+        WL_ALLOC(w->d_guard, tot);
+    }
+#undef WL_ALLOC
+#define WL_TRY(expr)                                                                          \
+    do {                                                                                      \
+        cudaError_t e__ = (expr);                                                             \
+        if (e__ != cudaSuccess) { ctx->error = std::string(#expr) + ": " + cudaGetErrorString(e__); return fail(PHMM_ERR_CUDA); } \
+    } while (0)
+    cudaStream_t st = ctx->stream;
+    const uint8_t *pools[5] = {fb->rs, fb->q, fb->i, fb->d, fb->c};
+    int64_t h2d = 0;
+    if (pool_len > 0)
+        for (int k = 0; k < 5; ++k) {
+            WL_TRY(cudaMemcpyAsync(w->d_pool + k * w->pool_stride, pools[k] + P.pool_lo, (size_t)pool_len, cudaMemcpyHostToDevice, st));
+            h2d += pool_len;
+        }
+    WL_TRY(cudaMemcpyAsync(w->d_stream, P.stream.data(), P.stream.size(), cudaMemcpyHostToDevice, st));
+    WL_TRY(cudaMemcpyAsync(w->d_hap_len, P.hap_len.data(), P.hap_len.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    if (!P.reads.empty())
+        WL_TRY(cudaMemcpyAsync(w->d_reads, P.reads.data(), P.reads.size() * sizeof(ReadRec), cudaMemcpyHostToDevice, st));
+    h2d += (int64_t)P.stream.size() + (int64_t)P.hap_len.size() * 4 + (int64_t)P.reads.size() * sizeof(ReadRec);
+    std::vector<int32_t> ints(INTS_TOTAL, 0);
+    for (size_t c = 0; c < P.classes.size(); ++c) {
+        if (!P.classes[c].tasks.empty())
+            WL_TRY(cudaMemcpyAsync(w->d_tasks + w->classes[c].task_off, P.classes[c].tasks.data(),
+                                   P.classes[c].tasks.size() * sizeof(Task), cudaMemcpyHostToDevice, st));
+        h2d += (int64_t)P.classes[c].tasks.size() * sizeof(Task);
+        ints[INTS_NTASKS + c] = w->classes[c].ntasks;
+    }
+    WL_TRY(cudaMemcpyAsync(w->d_ints, ints.data(), INTS_TOTAL * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    WL_TRY(cudaMemsetAsync(w->d_raw64, 0, (size_t)std::max<int64_t>(1, P.n_pairs) * sizeof(double), st));
+    WL_TRY(cudaMemsetAsync(w->d_rescued, 0, (size_t)std::max<int64_t>(1, P.n_pairs), st));
+    WL_TRY(cudaStreamSynchronize(st));
+#undef WL_TRY
+    w->h2d_bytes = h2d;
+    // host copies of the bulky plan parts are no longer needed
+    std::vector<uint8_t>().swap(P.stream);
+    for (auto &cp : P.classes) std::vector<Task>().swap(cp.tasks);
+    *out = w;
+    return PHMM_OK;
+}
+
+extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *stats)
+{
+    if (!ctx || !w || w->ctx != ctx) return PHMM_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const HostTables &t = host_tables();
+    const Plan &P = w->plan;
+    const bool fast32 = ctx->fp32_fast != 0, fast64 = ctx->fp64_fast != 0;
+    const int mode = w->precision;
+    int launches = 0;
+
+    // queue heads and list counters back to zero
+    CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_COUNTER, 0, 64 * sizeof(int32_t), st));
+    CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_RESC, 0, 64 * sizeof(int32_t), st));
+
+    KernelParams<float> pf;
+    memset(&pf, 0, sizeof pf);
+    pf.rs = w->d_pool; pf.q = w->d_pool + w->pool_stride; pf.i = w->d_pool + 2 * w->pool_stride;
+    pf.d = w->d_pool + 3 * w->pool_stride; pf.c = w->d_pool + 4 * w->pool_stride;
+    pf.reads = w->d_reads; pf.stream = w->d_stream; pf.hap_len = w->d_hap_len;
+    pf.ph2pr = ctx->d_ph2pr_f; pf.mm = ctx->d_mm_f;
+    pf.init_const = t.init_f; pf.log10_init = t.log10_init_f;
+    pf.out = w->d_out; pf.raw32 = w->d_raw32; pf.raw64 = w->d_raw64; pf.rescued = w->d_rescued;
+    pf.resc = w->d_resc; pf.resc_count = w->d_ints + INTS_RESC;
+    pf.guard = w->d_guard; pf.guard_count = w->d_ints + INTS_GUARD;
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) pf.resc_off[k] = w->resc_off[k];
+    pf.mode = mode;
+    {
+        // guard band of the fast kernel: |contracted - unfused| <= ~(5 (R + H)) ulp relative on an
+        // all-positive recurrence; 8x that, and never less than 2^-7
+        const double rel = std::max(1.0 / 128, 40.0 * (P.max_rslen + P.max_haplen) * 5.96e-8);
+        pf.guard_lo = (float)(1e-28 * (1.0 - rel));
+        pf.guard_hi = (float)(1e-28 * (1.0 + rel));
+    }
+    KernelParams<double> pd;
+    memset(&pd, 0, sizeof pd);
+    pd.rs = pf.rs; pd.q = pf.q; pd.i = pf.i; pd.d = pf.d; pd.c = pf.c;
+    pd.reads = pf.reads; pd.stream = pf.stream; pd.hap_len = pf.hap_len;
+    pd.ph2pr = ctx->d_ph2pr_d; pd.mm = ctx->d_mm_d;
+    pd.init_const = t.init_d; pd.log10_init = t.log10_init_d;
+    pd.out = w->d_out; pd.raw32 = w->d_raw32; pd.raw64 = w->d_raw64; pd.rescued = w->d_rescued;
+    pd.mode = mode;
+
+    auto grid_for = [&](const void *kernel, int64_t ntasks) -> int {
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, WARPS_PER_BLOCK * 32, 0) != cudaSuccess || nb < 1) nb = 1;
+        const int64_t full = (int64_t)nb * ctx->sm_count;
+        const int64_t want = (ntasks + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
+        return (int)std::max<int64_t>(1, std::min(full, want));
+    };
+    int counter_slot = 0;
+
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev[0], st));
+    // ---- main pass over the planned tasks ---------------------------------------------------
+    for (size_t c = 0; c < w->classes.size(); ++c) {
+        const ClassDev &cd = w->classes[c];
+        if (cd.ntasks == 0) continue;
+        if (counter_slot >= 60) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
+        if (mode == 2) {
+            KernelF64 k = lookup_f64(cd.kc.kh, fast64);
+            if (!k || cd.kc.vl != 1 || cd.kc.lanes != 32) { ctx->error = "no FP64 kernel for class"; return PHMM_ERR_ARG; }
+            pd.tasks = w->d_tasks + cd.task_off;
+            pd.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
+            pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
+            k<<<grid_for((const void *)k, cd.ntasks), WARPS_PER_BLOCK * 32, 0, st>>>(pd);
+        } else {
+            KernelF32 k = lookup_f32(cd.kc, fast32);
+            if (!k) { ctx->error = "no FP32 kernel for class"; return PHMM_ERR_ARG; }
+            pf.tasks = w->d_tasks + cd.task_off;
+            pf.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
+            pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
+            k<<<grid_for((const void *)k, cd.ntasks), WARPS_PER_BLOCK * 32, 0, st>>>(pf);
+        }
+        CUDA_TRY(ctx, cudaGetLastError());
+        ++launches;
+    }
+    // ---- fast kernel only: near-threshold pairs re-decided by the bit-exact scalar kernel -------
+    if (mode == 0 && fast32) {
+        for (int kh = 1; kh <= MAX_KH_SCALAR; ++kh) {
+            if (w->resc_cap[kh] == 0) continue;
+            KernelF32 k = lookup_f32s_f0(kh);
+            pf.tasks = w->d_guard + w->resc_off[kh];
+            pf.ntasks_ptr = w->d_ints + INTS_GUARD + kh;
+            pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
+            // the exact kernel never takes the guard branch (FAST = false)
+            k<<<grid_for((const void *)k, std::min<int64_t>(w->resc_cap[kh], 4096)), WARPS_PER_BLOCK * 32, 0, st>>>(pf);
+            CUDA_TRY(ctx, cudaGetLastError());
+            ++launches;
+        }
+    }
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev[1], st));
+    // ---- FP64 rescue (IntelPairHmmCSource.cpp:73-75) --------------------------------------------
+    if (mode == 0) {
+        for (int kh = 1; kh <= MAX_KH_SCALAR; ++kh) {
+            if (w->resc_cap[kh] == 0) continue;
+            KernelF64 k = lookup_f64(kh, fast64);
+            pd.tasks = w->d_resc + w->resc_off[kh];
+            pd.ntasks_ptr = w->d_ints + INTS_RESC + kh;
+            pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
+            k<<<grid_for((const void *)k, w->resc_cap[kh]), WARPS_PER_BLOCK * 32, 0, st>>>(pd);
+            CUDA_TRY(ctx, cudaGetLastError());
+            ++launches;
+        }
+    }
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev[2], st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+
+    int32_t counts[32];
+    CUDA_TRY(ctx, cudaMemcpy(counts, w->d_ints + INTS_RESC, sizeof counts, cudaMemcpyDeviceToHost));
+    int64_t nres = 0, nguard = 0;
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nres += counts[k]; nguard += counts[16 + k]; }
+    w->last_rescued = nres;
+    w->last_guard = nguard;
+    if (stats) {
+        memset(stats, 0, sizeof *stats);
+        stats->n_pairs = w->n_pairs;
+        stats->n_cells = w->n_cells;
+        stats->n_rescued = nres;
+        stats->n_guard = nguard;
+        stats->n_launches = launches;
+        stats->n_classes = (int32_t)w->classes.size();
+        for (auto &cd : w->classes) stats->n_tasks += cd.ntasks;
+        stats->h2d_bytes = w->h2d_bytes;
+        cudaEventElapsedTime(&stats->ms_fp32, ctx->ev[0], ctx->ev[1]);
+        cudaEventElapsedTime(&stats->ms_fp64, ctx->ev[1], ctx->ev[2]);
+        cudaEventElapsedTime(&stats->ms_total, ctx->ev[0], ctx->ev[2]);
+    }
+    return PHMM_OK;
+}
+
+extern "C" int phmm_workload_results(phmm_ctx *ctx, phmm_workload *w, double *out, float *raw32, double *raw64,
+                                     uint8_t *rescued)
+{
+    if (!ctx || !w || w->ctx != ctx) return PHMM_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)w->n_pairs;
+    if (n == 0) return PHMM_OK;
+    if (out) CUDA_TRY(ctx, cudaMemcpyAsync(out, w->d_out, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (raw32) CUDA_TRY(ctx, cudaMemcpyAsync(raw32, w->d_raw32, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (raw64) CUDA_TRY(ctx, cudaMemcpyAsync(raw64, w->d_raw64, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (rescued) CUDA_TRY(ctx, cudaMemcpyAsync(rescued, w->d_rescued, n, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return PHMM_OK;
+}
+
+// ============================================================================================
+// host-buffer entry points
+// ============================================================================================
+static double wall_ms()
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+
+extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, double *out, phmm_stats *stats)
+{
+    if (!ctx || !fb) return PHMM_ERR_ARG;
+    phmm_workload *w = nullptr;
+    const double t0 = wall_ms();
+    int rc = phmm_workload_create(ctx, fb, &w);
+    if (rc != PHMM_OK) return rc;
+    const double t1 = wall_ms();
+    phmm_stats s;
+    rc = phmm_workload_run(ctx, w, &s);
+    if (rc == PHMM_OK && w->n_pairs > 0 && !out) { ctx->error = "NULL output"; rc = PHMM_ERR_ARG; }
+    const double t2 = wall_ms();
+    if (rc == PHMM_OK) rc = phmm_workload_results(ctx, w, out, nullptr, nullptr, nullptr);
+    const double t3 = wall_ms();
+    if (stats && rc == PHMM_OK) {
+        *stats = s;
+        stats->ms_h2d = (float)(t1 - t0);      // plan + upload
+        stats->ms_d2h = (float)(t3 - t2);
+        stats->d2h_bytes = w->n_pairs * (int64_t)sizeof(double);
+    }
+    phmm_workload_destroy(w);
+    return rc;
+}
+
+namespace {
+// Growable flat batches built from pointer-based inputs, de-duplicating strings by address.
+struct FlatBuilder {
+    ParsedBatches b;
+    struct ReadKey {
+        const void *p[5];
+        int len;
+        bool operator==(const ReadKey &o) const { return memcmp(p, o.p, sizeof p) == 0 && len == o.len; }
+    };
+    struct ReadKeyHash {
+        size_t operator()(const ReadKey &k) const
+        {
+            size_t h = (size_t)k.len * 0x9E3779B97F4A7C15ull;
+            for (int j = 0; j < 5; ++j) h = (h ^ (size_t)k.p[j]) * 0x100000001B3ull;
+            return h;
+        }
+    };
+    struct HapKey {
+        const void *p;
+        int len;
+        bool operator==(const HapKey &o) const { return p == o.p && len == o.len; }
+    };
+    struct HapKeyHash {
+        size_t operator()(const HapKey &k) const { return ((size_t)k.p * 0x9E3779B97F4A7C15ull) ^ (size_t)k.len; }
+    };
+    std::unordered_map<ReadKey, int64_t, ReadKeyHash> read_at;   // string addresses -> pool offset
+    std::unordered_map<HapKey, int64_t, HapKeyHash> hap_at;
+
+    int64_t add_read(const char *rs, const char *q, const char *i, const char *d, const char *c, int len)
+    {
+        const ReadKey key{{rs, q, i, d, c}, len};
+        auto it = read_at.find(key);
+        if (it != read_at.end()) return it->second;
+        const int64_t off = (int64_t)b.rs.size();
+        b.rs.insert(b.rs.end(), (const uint8_t *)rs, (const uint8_t *)rs + len);
+        b.q.insert(b.q.end(), (const uint8_t *)q, (const uint8_t *)q + len);
+        b.i.insert(b.i.end(), (const uint8_t *)i, (const uint8_t *)i + len);
+        b.d.insert(b.d.end(), (const uint8_t *)d, (const uint8_t *)d + len);
+        b.c.insert(b.c.end(), (const uint8_t *)c, (const uint8_t *)c + len);
+        read_at.emplace(key, off);
+        return off;
+    }
+    int64_t add_hap(const char *hap, int len)
+    {
+        const HapKey key{hap, len};
+        auto it = hap_at.find(key);
+        if (it != hap_at.end()) return it->second;
+        const int64_t off = (int64_t)b.hap.size();
+        b.hap.insert(b.hap.end(), (const uint8_t *)hap, (const uint8_t *)hap + len);
+        hap_at.emplace(key, off);
+        return off;
+    }
+};
+}  // namespace
+
+extern "C" int phmm_compute_batches(phmm_ctx *ctx, const phmm_batch *batches, int64_t n_batches)
+{
+    if (!ctx || n_batches < 0 || (n_batches && !batches)) return PHMM_ERR_ARG;
+    FlatBuilder fbld;
+    ParsedBatches &b = fbld.b;
+    int64_t npairs = 0;
+    for (int64_t k = 0; k < n_batches; ++k) {
+        const phmm_batch &bt = batches[k];
+        if (bt.num_reads < 0 || bt.num_haps < 0 || (bt.num_reads && !bt.reads) || (bt.num_haps && !bt.haps)) {
+            ctx->error = "malformed batch";
+            return PHMM_ERR_ARG;
+        }
+        b.batch_num_reads.push_back(bt.num_reads);
+        b.batch_num_haps.push_back(bt.num_haps);
+        for (int r = 0; r < bt.num_reads; ++r) {
+            const phmm_read &rd = bt.reads[r];
+            if (rd.length <= 0) { ctx->error = "read of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+            if (!rd.bases || !rd.q || !rd.i || !rd.d || !rd.c) { ctx->error = "NULL read field"; return PHMM_ERR_ARG; }
+            b.read_len.push_back(rd.length);
+            b.read_off.push_back(fbld.add_read(rd.bases, rd.q, rd.i, rd.d, rd.c, rd.length));
+        }
+        for (int h = 0; h < bt.num_haps; ++h) {
+            const phmm_hap &hp = bt.haps[h];
+            if (hp.length <= 0) { ctx->error = "haplotype of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+            if (!hp.bases) { ctx->error = "NULL haplotype"; return PHMM_ERR_ARG; }
+            b.hap_len.push_back(hp.length);
+            b.hap_off.push_back(fbld.add_hap(hp.bases, hp.length));
+        }
+        if ((int64_t)bt.num_reads * bt.num_haps > 0 && !bt.results) { ctx->error = "NULL results"; return PHMM_ERR_ARG; }
+        npairs += (int64_t)bt.num_reads * bt.num_haps;
+    }
+    b.finish();
+    std::vector<double> out((size_t)npairs);
+    int rc = phmm_compute_flat(ctx, &b.view, out.data(), nullptr);
+    if (rc != PHMM_OK) return rc;
+    int64_t p = 0;
+    for (int64_t k = 0; k < n_batches; ++k) {
+        const int64_t n = (int64_t)batches[k].num_reads * batches[k].num_haps;
+        if (n) memcpy(batches[k].results, out.data() + p, (size_t)n * sizeof(double));
+        p += n;
+    }
+    return PHMM_OK;
+}
+
+// computelikelihoodsboth's argument list.  The driver fills its slab read-major with pointers
+// into per-read / per-haplotype strings (PairHMMUnitTest_orig.cpp:284-297); consecutive pairs
+// with the same `rs` pointer become one read's haplotype list, and consecutive reads with the
+// same haplotype pointer list fold back into the reads x haplotypes batch they came from.
+extern "C" int phmm_compute_pairs(phmm_ctx *ctx, const phmm_testcase *tc, double *out, int64_t n)
+{
+    if (!ctx || n < 0 || (n && (!tc || !out))) return PHMM_ERR_ARG;
+    if (n == 0) return PHMM_OK;
+    FlatBuilder fbld;
+    ParsedBatches &b = fbld.b;
+    int64_t k = 0;
+    int64_t prev_first = -1, prev_nh = 0;      // pair index / size of the previous read's hap list
+    while (k < n) {
+        const phmm_testcase &t0 = tc[k];
+        if (!t0.rs || !t0.q || !t0.i || !t0.d || !t0.c) { ctx->error = "NULL read field in testcase"; return PHMM_ERR_ARG; }
+        if (t0.rslen <= 0) { ctx->error = "rslen <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+        int64_t k1 = k;
+        while (k1 < n && tc[k1].rs == t0.rs && tc[k1].rslen == t0.rslen && tc[k1].q == t0.q && tc[k1].i == t0.i &&
+               tc[k1].d == t0.d && tc[k1].c == t0.c)
+            ++k1;
+        const int64_t nh = k1 - k;
+        bool same = (prev_first >= 0 && nh == prev_nh);
+        for (int64_t j = 0; same && j < nh; ++j)
+            same = tc[k + j].hap == tc[prev_first + j].hap && tc[k + j].haplen == tc[prev_first + j].haplen;
+        if (same) {
+            b.batch_num_reads.back() += 1;
+        } else {
+            b.batch_num_reads.push_back(1);
+            b.batch_num_haps.push_back((int32_t)nh);
+            for (int64_t j = 0; j < nh; ++j) {
+                const phmm_testcase &t = tc[k + j];
+                if (!t.hap) { ctx->error = "NULL haplotype in testcase"; return PHMM_ERR_ARG; }
+                if (t.haplen <= 0) { ctx->error = "haplen <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+                b.hap_len.push_back(t.haplen);
+                b.hap_off.push_back(fbld.add_hap(t.hap, t.haplen));
+            }
+        }
+        b.read_len.push_back(t0.rslen);
+        b.read_off.push_back(fbld.add_read(t0.rs, t0.q, t0.i, t0.d, t0.c, t0.rslen));
+        prev_first = k;
+        prev_nh = nh;
+        k = k1;
+    }
+    b.finish();
+    return phmm_compute_flat(ctx, &b.view, out, nullptr);
+}
+
+// ============================================================================================
+// measurement helpers
+// ============================================================================================
+extern "C" int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s, float *ms_out)
+{
+    if (!ctx || !lane_ops_per_s) return PHMM_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const int grid = ctx->sm_count * 8, iters = 4096;
+    double ops_per_thread = 0;
+    CUDA_TRY(ctx, launch_pipe_bench(which, ctx->d_bench, grid, 64, ctx->stream, &ops_per_thread));   // warm-up
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; ++rep) {
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+        CUDA_TRY(ctx, launch_pipe_bench(which, ctx->d_bench, grid, iters, ctx->stream, &ops_per_thread));
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        float ms = 0;
+        CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+        best = std::min(best, ms);
+    }
+    *lane_ops_per_s = ops_per_thread * 256.0 * grid / (best * 1e-3);
+    if (ms_out) *ms_out = best;
+    return PHMM_OK;
+}
+
+// Plan-only summary (no device needed): used by the CPU test-suite to check the host logic.
+extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int packed, int seg_cols,
+                                 int64_t *info /* [8 + 4 * 16] */, uint8_t *pair_cover /* [n_pairs] or NULL */)
+{
+    if (!fb || !info) return PHMM_ERR_ARG;
+    PlanOptions o;
+    o.precision = precision;
+    o.packed = packed;
+    o.seg_cols = seg_cols;
+    Plan P;
+    std::string err;
+    int rc = build_plan(*fb, o, &P, &err);
+    if (rc != PHMM_OK) return rc;
+    info[0] = P.n_pairs; info[1] = P.n_cells; info[2] = (int64_t)P.classes.size();
+    info[3] = (int64_t)P.stream.size(); info[4] = P.max_rslen; info[5] = P.max_haplen;
+    int64_t ntasks = 0;
+    for (size_t c = 0; c < P.classes.size() && c < 16; ++c) {
+        info[8 + 4 * c + 0] = P.classes[c].kc.kh;
+        info[8 + 4 * c + 1] = P.classes[c].kc.lanes;
+        info[8 + 4 * c + 2] = P.classes[c].kc.vl;
+        info[8 + 4 * c + 3] = (int64_t)P.classes[c].tasks.size();
+    }
+    for (auto &cp : P.classes) ntasks += (int64_t)cp.tasks.size();
+    info[6] = ntasks;
+    if (pair_cover) {
+        // walk every task the way the kernel does and count how often each pair is produced
+        for (auto &cp : P.classes)
+            for (auto &t : cp.tasks) {
+                int nh = 0;
+                for (int64_t col = 0; col < t.ncols; ++nh) col += P.hap_len[t.hap0 + nh] + 1;
+                for (int g = 0; g < cp.kc.group(); ++g) {
+                    if (t.read[g] < 0) continue;
+                    const ReadRec &rr = P.reads[t.read[g]];
+                    if (rr.len > cp.kc.capacity()) return PHMM_ERR_ARG;
+                    for (int j = 0; j < nh; ++j) pair_cover[rr.out_base + t.out0 + j]++;
+                }
+            }
+    }
+    return PHMM_OK;
+}

@@ -1,0 +1,94 @@
+// Internal host-side declarations of libphmm_cuda (planner, tables, kernel lookup).
+#ifndef PHMM_HOST_H
+#define PHMM_HOST_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/phmm_cuda.h"
+#include "phmm_types.h"
+
+namespace phmm {
+
+// ---- probability tables (phmm_tables.cpp) ---------------------------------------------------
+static const int MM_REACHABLE = (127 * 128) / 2 + 127 + 1;   // 8256: max index with quals <= 127
+struct HostTables {
+    float ph2pr_f[128];
+    double ph2pr_d[128];
+    std::vector<float> mm_f;     // [MM_REACHABLE]
+    std::vector<double> mm_d;
+    float init_f, log10_init_f;
+    double init_d, log10_init_d;
+};
+const HostTables &host_tables();
+
+// ---- planner (phmm_plan.cpp) -------------------------------------------------------------------
+struct PlanOptions {
+    int precision = 0;        // PHMM_OPT_PRECISION
+    int packed = 1;           // PHMM_OPT_PACKED
+    int seg_cols = 0;         // 0 = adaptive
+    int resident_warps = 2368;   // warps the device keeps in flight (for adaptive run sizing)
+    int force_kh = 0, force_lanes = 0;   // debugging / benchmarking: pin the kernel class
+    double step_overhead = 0.9;  // per-step fixed cost in units of one register-tile row
+};
+
+struct ClassPlan {
+    KClass kc;
+    std::vector<Task> tasks;   // sorted by decreasing cost
+    int64_t cells = 0;
+    int64_t pairs = 0;
+};
+
+struct Plan {
+    std::vector<ReadRec> reads;
+    std::vector<uint8_t> stream;         // coded haplotype columns (+ STREAM_SLACK)
+    std::vector<int32_t> hap_len;        // stream order, + 1 slack entry
+    std::vector<ClassPlan> classes;
+    int64_t n_pairs = 0, n_cells = 0;
+    int64_t pool_lo = 0, pool_hi = 0;    // referenced byte range of the read pools
+    int64_t resc_cap[MAX_KH_SCALAR + 1]; // pairs whose read falls in each scalar class
+    int max_rslen = 0, max_haplen = 0;
+};
+
+// Chooses the kernel class for a read length; returns false when no single-pass class fits.
+bool choose_class(int rslen, const PlanOptions &opt, KClass *kc);
+// Builds the plan; on failure returns a PHMM_ERR_* code and fills `err`.
+int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, std::string *err);
+
+// ---- kernels (phmm_inst_*.cu, phmm_microbench.cu) -------------------------------------------
+typedef void (*KernelF32)(const KernelParams<float>);
+typedef void (*KernelF64)(const KernelParams<double>);
+KernelF32 lookup_f32p_l32_f0(int kh);
+KernelF32 lookup_f32p_l32_f1(int kh);
+KernelF32 lookup_f32p_l16_f0(int kh);
+KernelF32 lookup_f32p_l16_f1(int kh);
+KernelF32 lookup_f32p_l8_f0(int kh);
+KernelF32 lookup_f32p_l8_f1(int kh);
+KernelF32 lookup_f32s_f0(int kh);
+KernelF32 lookup_f32s_f1(int kh);
+KernelF64 lookup_f64_f0(int kh);
+KernelF64 lookup_f64_f1(int kh);
+KernelF32 lookup_f32(const KClass &kc, bool fast);
+KernelF64 lookup_f64(int kh, bool fast);
+cudaError_t launch_pipe_bench(int which, float *out, int grid, int iters, cudaStream_t st,
+                              double *ops_per_thread);
+
+// ---- text parser (phmm_parse.cpp) -----------------------------------------------------------
+struct ParsedBatches {
+    std::vector<int32_t> batch_num_reads, batch_num_haps, read_len, hap_len;
+    std::vector<int64_t> read_off, hap_off;
+    std::vector<uint8_t> rs, q, i, d, c, hap;
+    phmm_flat_batches view;
+    void finish();     // fills `view` from the vectors
+};
+
+}  // namespace phmm
+
+struct phmm_parsed {
+    phmm::ParsedBatches b;
+};
+
+#endif

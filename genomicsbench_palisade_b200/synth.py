@@ -196,7 +196,7 @@ def c5_skewed(n_pairs=10_000_000, seed=SEED0 + 5):
                      foreign_subst=0.25)
 
 
-def edge_cases(seed=SEED0 + 9):
+def edge_cases(seed=SEED0 + 9, max_read_len=None):
     """Small adversarial batches: R > H, length-1 reads and haplotypes, N bases on both sides,
     bytes outside ACGTN (the reference maps them to 'A', `pairhmm_common.h:27,34-38`), reads
     whose length sits on every register-tile boundary, extreme quality values."""
@@ -211,6 +211,8 @@ def edge_cases(seed=SEED0 + 9):
     # every read length 1..70 and around multiples of 32 against short/long haplotypes
     lens = list(range(1, 71)) + [95, 96, 97, 127, 128, 129, 159, 160, 161, 191, 192, 193,
                                  223, 224, 225, 254, 255, 256, 257, 300, 511, 512, 513, 700]
+    if max_read_len is not None:
+        lens = [n for n in lens if n <= max_read_len]
     reads = [read(n) for n in lens]
     haps = [_rand_bases(rng, n, 0.05) for n in (1, 2, 3, 31, 32, 33, 64, 100, 255, 256, 257, 600)]
     batches.append((reads, haps))

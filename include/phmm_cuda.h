@@ -1,0 +1,219 @@
+/*
+ * phmm_cuda.h -- C ABI of libphmm_cuda.so, the B200 (sm_100a) pair-HMM forward engine.
+ *
+ * Drop-in boundary for the GenomicsBench `phmm` hot path.  Reference paths below are relative
+ * to /root/reference.  The reference library behind this boundary is libgkl_pairhmm_c
+ * (tools/GKL/src/main/native/pairhmm/IntelPairHmmCSource.cpp), which the benchmark driver
+ * links with -lgkl_pairhmm_c (benchmarks/phmm/Makefile:32-34).
+ *
+ * Three layers, all in this one library:
+ *   1. the reference's own four C++-linkage symbols (section "legacy symbols" at the end), so
+ *      the unmodified driver object links against libphmm_cuda.so instead of libgkl_pairhmm_c;
+ *   2. plain `extern "C"` entry points taking HOST buffers (blocking, results written when they
+ *      return) -- what a cgo / JNI / ctypes binding would call;
+ *   3. a device-resident workload API (plan + upload once, run many times) used for kernel-only
+ *      timing and by the rewritten driver's pipeline.
+ *
+ * There is no CPU fallback: every compute entry point returns PHMM_ERR_CUDA when no sm_100
+ * device is usable.
+ */
+#ifndef PHMM_CUDA_H
+#define PHMM_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PHMM_ABI_VERSION 1
+
+/* ---- status codes (the reference defines none: it asserts / exit(0)s) ---- */
+#define PHMM_OK              0
+#define PHMM_ERR_ARG         1   /* NULL pointer, negative count, inconsistent table          */
+#define PHMM_ERR_EMPTY_SEQ   2   /* rslen == 0 or haplen == 0: undefined in the reference      */
+                                 /* (division by haplen, avx-pairhmm-template.h:86)            */
+#define PHMM_ERR_TOO_LONG    3   /* read or haplotype longer than PHMM_MAX_SEQ_LEN             */
+#define PHMM_ERR_CUDA        4   /* no usable device / CUDA runtime error (see last_error)     */
+#define PHMM_ERR_NOMEM       5
+#define PHMM_ERR_PARSE       6   /* malformed text input                                       */
+#define PHMM_ERR_IO          7
+
+/* Declared limits of the reference: MAX_READ_LENGTH / MAX_HAP_LENGTH = 32K
+ * (benchmarks/phmm/PairHMMUnitTest.h:35-36). */
+#define PHMM_MAX_SEQ_LEN 32768
+
+/* ---- the reference's per-pair descriptor ------------------------------------------------
+ * Layout-identical to `testcase` (benchmarks/phmm/pairhmm_common.h:20-24,
+ * tools/GKL/src/main/native/pairhmm/pairhmm_common.h:20-24): q/i/d/c are Phred values already
+ * normalised by the driver (PairHMMUnitTest_orig.cpp:88-92,120-123), rs/hap are ASCII bases,
+ * none of them NUL-terminated beyond rslen/haplen. */
+typedef struct {
+    int rslen, haplen;
+    const char *q, *i, *d, *c;
+    const char *hap, *rs;
+} phmm_testcase;
+
+/* ---- the reference driver's batch containers ----------------------------------------------
+ * Field-for-field the plaintext part of shacc_pairhmm::Read / Haplotype / Batch
+ * (tools/GKL/src/main/native/pairhmm/shacc_pairhmm.h:12-35; benchmarks/phmm/shacc_pairhmm.h:14-46
+ * adds HE ciphertext members that are out of scope).  A batch is evaluated all-pairs and
+ * results[r * num_haps + h] receives the log10 likelihood (PairHMMUnitTest_orig.cpp:284-299). */
+typedef struct {
+    int length;
+    const char *bases, *q, *i, *d, *c;
+} phmm_read;
+
+typedef struct {
+    int length;
+    const char *bases;
+} phmm_hap;
+
+typedef struct {
+    int num_reads, num_haps;
+    const phmm_read *reads;
+    const phmm_hap *haps;
+    double *results;              /* num_reads * num_haps doubles, caller-owned */
+} phmm_batch;
+
+/* ---- flat structure-of-arrays batches -------------------------------------------------------
+ * What the rewritten driver's parser produces directly (no per-string heap allocation) and
+ * what a binding for a GC'd language can build without pinning thousands of small objects:
+ * six byte pools plus offset tables.  Reads of batch 0 come first, then batch 1, ...; the same
+ * for haplotypes.  Read r occupies [read_off[r], read_off[r] + read_len[r]) in EACH of the five
+ * read pools.  Results are batch-major, then r * num_haps + h, exactly the order in which the
+ * reference fills its per-batch `results` arrays. */
+typedef struct {
+    int64_t n_batches;
+    const int32_t *batch_num_reads;     /* [n_batches] */
+    const int32_t *batch_num_haps;      /* [n_batches] */
+    int64_t n_reads;
+    const int32_t *read_len;            /* [n_reads] */
+    const int64_t *read_off;            /* [n_reads] */
+    const uint8_t *rs, *q, *i, *d, *c;  /* read pools */
+    int64_t n_haps;
+    const int32_t *hap_len;             /* [n_haps] */
+    const int64_t *hap_off;             /* [n_haps] */
+    const uint8_t *hap;                 /* haplotype pool */
+} phmm_flat_batches;
+
+/* ---- options ------------------------------------------------------------------------------ */
+#define PHMM_OPT_PRECISION   1   /* 0 both: FP32 + FP64 rescue (computelikelihoodsboth, default)
+                                    1 FP32 only (computelikelihoodsfloat, :89-99)
+                                    2 FP64 only (computelikelihoodsdouble, :103-114)          */
+#define PHMM_OPT_FP32_KERNEL 2   /* 0 bit-exact: unfused mul/add in the reference's association
+                                      order, raw FP32 sums identical to the AVX code
+                                    1 fast: FMA-contracted; pairs whose sum lands in a guard band
+                                      around MIN_ACCEPTED are re-decided by the bit-exact kernel,
+                                      so the FP64-rescue set stays identical                    */
+#define PHMM_OPT_FP64_KERNEL 3   /* 0 bit-exact (unfused), 1 FMA-contracted (|rel err| ~1e-13)  */
+#define PHMM_OPT_SEG_COLS    4   /* target haplotype-stream columns per task (load balancing)    */
+#define PHMM_OPT_PACKED      5   /* 1 (default) FP32 kernel uses Blackwell packed f32x2 math
+                                    (FMUL2/FFMA2), 0 scalar FMUL/FADD/FFMA                       */
+#define PHMM_OPT_FORCE_CLASS 6   /* benchmarking: pin the kernel class, value = kh << 8 | lanes
+                                    (0 = choose per read length); also env PHMM_FORCE_CLASS=kh,lanes */
+
+typedef struct phmm_ctx phmm_ctx;
+typedef struct phmm_workload phmm_workload;
+
+/* Statistics of one run (all counts are for the last call on that workload). */
+typedef struct {
+    int64_t n_pairs;
+    int64_t n_cells;            /* sum rslen * haplen, rescued pairs counted once              */
+    int64_t n_rescued;          /* pairs re-run in FP64 (FP32 sum < MIN_ACCEPTED = 1e-28f)     */
+    int64_t n_rescued_cells;
+    int64_t n_guard;            /* fast kernel only: pairs re-decided by the bit-exact kernel  */
+    int64_t n_tasks;            /* warp tasks over all kernel classes                          */
+    int64_t h2d_bytes, d2h_bytes;
+    int32_t n_launches;         /* kernels launched by the last run                            */
+    int32_t n_classes;          /* distinct (rows-per-lane, lanes-per-read) kernel classes     */
+    float   ms_fp32;            /* CUDA-event time of the FP32 kernels of the last run         */
+    float   ms_fp64;            /* ... of the FP64 rescue kernels                              */
+    float   ms_total;           /* first launch to last kernel end                            */
+    float   ms_h2d, ms_d2h;     /* host-buffer entry points only                               */
+} phmm_stats;
+
+/* ---- lifetime ------------------------------------------------------------------------------
+ * phmm_create replaces initPairHMM (IntelPairHmmCSource.cpp:29-51): instead of cpuid dispatch it
+ * binds a CUDA device, generates the Context<float>/Context<double> probability tables
+ * (Context.h:42-61,101-114,141-154) on the host with the host libm and uploads them. */
+int phmm_create(int device, phmm_ctx **ctx);
+int phmm_destroy(phmm_ctx *ctx);
+int phmm_set_option(phmm_ctx *ctx, int option, int64_t value);
+int64_t phmm_get_option(const phmm_ctx *ctx, int option);
+const char *phmm_last_error(const phmm_ctx *ctx);   /* ctx may be NULL: last create() failure */
+int phmm_abi_version(void);
+int phmm_device_count(void);
+
+/* ---- host-buffer entry points (blocking) --------------------------------------------------- */
+/* computelikelihoodsboth(testcase*, double*, int) (IntelPairHmmCSource.cpp:61-85): out[k] is the
+ * log10 likelihood of pair k, order preserved.  Pairs sharing rs/hap pointers (the driver's
+ * all-pairs slabs) are de-duplicated before upload. */
+int phmm_compute_pairs(phmm_ctx *ctx, const phmm_testcase *pairs, double *out, int64_t n);
+/* The reference driver's inner loop over batches (PairHMMUnitTest_orig.cpp:271-300) in one call. */
+int phmm_compute_batches(phmm_ctx *ctx, const phmm_batch *batches, int64_t n_batches);
+int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, double *out, phmm_stats *stats);
+
+/* ---- device-resident workloads -------------------------------------------------------------- */
+/* Plan (kernel classes, haplotype-stream segments, LPT-ordered warp tasks) and upload. */
+int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, phmm_workload **w);
+/* Launch the FP32 kernels and the FP64 rescue kernels on the context's stream and wait. */
+int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *stats);
+/* Copy results back: out = log10 likelihoods; the others may be NULL.  raw32 = FP32 sums scaled
+ * by 2^120 (what compute_full_prob_<float> returns), raw64 = FP64 sums scaled by 2^1020 for
+ * rescued pairs (0 elsewhere), rescued = 1 where the FP64 path produced `out`. */
+int phmm_workload_results(phmm_ctx *ctx, phmm_workload *w, double *out, float *raw32,
+                          double *raw64, uint8_t *rescued);
+int phmm_workload_destroy(phmm_workload *w);
+
+/* ---- host-side scheduler ---------------------------------------------------------------------
+ * Longest-processing-time-first assignment of n items (batches) with the given costs (cells) to
+ * `parts` devices; owner[k] in [0, parts).  Deterministic, so every rank computes the same map. */
+int phmm_partition_lpt(const int64_t *cost, int64_t n, int parts, int32_t *owner);
+
+/* ---- text input (the reference's on-disk format) ---------------------------------------------
+ * Parses what read_testfile / read_batch read (PairHMMUnitTest_orig.cpp:97-213) into flat
+ * batches owned by the returned handle; qualities are normalised as the driver does
+ * (`normalize`, :88-92: q floor 6, i/d/c floor 0, after subtracting 33). */
+typedef struct phmm_parsed phmm_parsed;
+int phmm_parse_file(const char *path, phmm_parsed **out, char *err, size_t err_len);
+int phmm_parse_buffer(const char *data, size_t len, phmm_parsed **out, char *err, size_t err_len);
+const phmm_flat_batches *phmm_parsed_batches(const phmm_parsed *p);
+void phmm_parsed_free(phmm_parsed *p);
+
+/* ---- measurement helpers ----------------------------------------------------------------------
+ * FP32 pipe microbenchmarks on the context's device, for the roofline denominator
+ * ("builder must measure an FFMA-only microbenchmark on the box").
+ * which: 0 FFMA, 1 FFMA2 (packed), 2 FMUL+FADD mix, 3 FMUL2+FADD mix, 4 DFMA.
+ * Returns lane-operations per second (an FMA counts as one operation). */
+int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s, float *ms);
+
+/* ---- test hooks (no device needed) ------------------------------------------------------------
+ * phmm_get_tables: the host-generated probability tables the library uploads (Context.h); returns
+ * the number of matchToMatchProb entries (8256).  consts_f/d = {INITIAL_CONSTANT, LOG10_INITIAL_CONSTANT}.
+ * phmm_plan_summary: runs the planner only.  info[0..6] = pairs, cells, classes, stream bytes,
+ * max rslen, max haplen, tasks; info[8 + 4c ..] = {kh, lanes, vl, tasks} of class c (c < 16);
+ * pair_cover[p] is incremented once for every task that produces pair p. */
+int phmm_get_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d, float *consts_f,
+                    double *consts_d);
+int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int packed, int seg_cols,
+                      int64_t *info, uint8_t *pair_cover);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+
+/* ---- legacy symbols ------------------------------------------------------------------------
+ * libphmm_cuda.so also defines, with C++ linkage and no header (the driver re-declares them,
+ * PairHMMUnitTest_orig.cpp:84-86), exactly the symbols libgkl_pairhmm_c exports:
+ *     void initPairHMM();                                           _Z11initPairHMMv
+ *     void computelikelihoodsboth(testcase*, double*, int);         _Z22computelikelihoodsbothP8testcasePdi
+ *     void computelikelihoodsfloat(testcase*, float*);              _Z23computelikelihoodsfloatP8testcasePf
+ *     void computelikelihoodsdouble(testcase*, double*);            _Z24computelikelihoodsdoubleP8testcasePd
+ *     uint8_t ConvertChar::conversionTable[255];                    _ZN11ConvertChar15conversionTableE
+ * (IntelPairHmmCSource.cpp:29,61,89,103; pairhmm_common.cc:3).  They bind device
+ * $PHMM_DEVICE (default 0), are thread-safe, and abort() with a message on error because the
+ * reference signatures have no way to report one. */
+
+#endif /* PHMM_CUDA_H */
