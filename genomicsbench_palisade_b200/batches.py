@@ -122,6 +122,22 @@ class FlatBatches:
                            self.rs, self.q, self.i, self.d, self.c,
                            self.hap_len[h_idx], self.hap_off[h_idx], self.hap, dict(self.meta))
 
+    def select_reads(self, keep):
+        """Drop reads where `keep` is False.  Returns (batches, pair_index) with pair_index[k] the
+        position of the new pair k in this object's pair order."""
+        keep = np.asarray(keep, bool)
+        brs, bos = self.batch_read_start, self.batch_out_start
+        bnr, idx = [], []
+        for b in range(self.n_batches):
+            nh = int(self.batch_num_haps[b])
+            k = np.nonzero(keep[brs[b]:brs[b + 1]])[0]
+            bnr.append(len(k))
+            idx.append((bos[b] + k[:, None] * nh + np.arange(nh)[None, :]).ravel())
+        fb = FlatBatches(bnr, self.batch_num_haps, self.read_len[keep], self.read_off[keep],
+                         self.rs, self.q, self.i, self.d, self.c, self.hap_len, self.hap_off, self.hap,
+                         dict(self.meta))
+        return fb, (np.concatenate(idx).astype(np.int64) if idx else np.zeros(0, np.int64))
+
     # ---- the reference's text format ----------------------------------------------------------
     def to_text(self) -> bytes:
         """Serialise in the reference's input format (`_orig.cpp:97-169`): qualities are

@@ -63,6 +63,9 @@ struct phmm_workload {
     double *d_out = nullptr, *d_raw64 = nullptr;
     float *d_raw32 = nullptr;
     uint8_t *d_rescued = nullptr;
+    double *d_scratch = nullptr;      // multi-pass kernels: boundary rows, one slot per resident warp
+    int64_t scratch_stride = 0;       // doubles per warp
+    int scratch_blocks = 0;           // grid cap of the multi-pass kernels
     int64_t last_rescued = 0, last_rescued_cells = 0, last_guard = 0;
 };
 
@@ -102,6 +105,7 @@ int dev_alloc(phmm_ctx *ctx, T **p, size_t n)
 namespace phmm {
 KernelF32 lookup_f32(const KClass &kc, bool fast)
 {
+    if (kc.longr) return lookup_f32_long(kc.vl == 2 ? (fast ? 1 : 0) : (fast ? 3 : 2));
     if (kc.vl == 1) return kc.lanes == 32 ? (fast ? lookup_f32s_f1(kc.kh) : lookup_f32s_f0(kc.kh)) : nullptr;
     switch (kc.lanes) {
     case 32: return fast ? lookup_f32p_l32_f1(kc.kh) : lookup_f32p_l32_f0(kc.kh);
@@ -258,6 +262,7 @@ extern "C" int phmm_workload_destroy(phmm_workload *w)
     cudaFree(w->d_pool); cudaFree(w->d_stream); cudaFree(w->d_hap_len); cudaFree(w->d_reads);
     cudaFree(w->d_tasks); cudaFree(w->d_resc); cudaFree(w->d_guard); cudaFree(w->d_ints);
     cudaFree(w->d_out); cudaFree(w->d_raw64); cudaFree(w->d_raw32); cudaFree(w->d_rescued);
+    cudaFree(w->d_scratch);
     delete w;
     return PHMM_OK;
 }
@@ -317,6 +322,13 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
     if (need_resc) {
         WL_ALLOC(w->d_resc, tot);
         WL_ALLOC(w->d_guard, tot);
+    }
+    if (P.long_max_cols > 0) {
+        // long reads may also come back as single-haplotype rescue / guard tasks
+        const int64_t cols = std::max<int64_t>(P.long_max_cols, P.max_haplen + 1) + 64;
+        w->scratch_stride = 6 * cols;
+        w->scratch_blocks = ctx->sm_count * 2;
+        WL_ALLOC(w->d_scratch, w->scratch_stride * w->scratch_blocks * WARPS_PER_BLOCK);
     }
 #undef WL_ALLOC
 #define WL_TRY(expr)                                                                          \
@@ -400,6 +412,8 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
     pd.init_const = t.init_d; pd.log10_init = t.log10_init_d;
     pd.out = w->d_out; pd.raw32 = w->d_raw32; pd.raw64 = w->d_raw64; pd.rescued = w->d_rescued;
     pd.mode = mode;
+    pf.scratch = reinterpret_cast<float *>(w->d_scratch); pf.scratch_stride = w->scratch_stride;
+    pd.scratch = w->d_scratch; pd.scratch_stride = w->scratch_stride;
 
     auto grid_for = [&](const void *kernel, int64_t ntasks) -> int {
         int nb = 0;
@@ -417,33 +431,39 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
         if (cd.ntasks == 0) continue;
         if (counter_slot >= 60) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
         if (mode == 2) {
-            KernelF64 k = lookup_f64(cd.kc.kh, fast64);
+            KernelF64 k = cd.kc.longr ? lookup_f64_long(fast64) : lookup_f64(cd.kc.kh, fast64);
             if (!k || cd.kc.vl != 1 || cd.kc.lanes != 32) { ctx->error = "no FP64 kernel for class"; return PHMM_ERR_ARG; }
             pd.tasks = w->d_tasks + cd.task_off;
             pd.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
             pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
-            k<<<grid_for((const void *)k, cd.ntasks), WARPS_PER_BLOCK * 32, 0, st>>>(pd);
+            int grid = grid_for((const void *)k, cd.ntasks);
+            if (cd.kc.longr) grid = std::min(grid, w->scratch_blocks);
+            k<<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pd);
         } else {
             KernelF32 k = lookup_f32(cd.kc, fast32);
             if (!k) { ctx->error = "no FP32 kernel for class"; return PHMM_ERR_ARG; }
             pf.tasks = w->d_tasks + cd.task_off;
             pf.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
             pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
-            k<<<grid_for((const void *)k, cd.ntasks), WARPS_PER_BLOCK * 32, 0, st>>>(pf);
+            int grid = grid_for((const void *)k, cd.ntasks);
+            if (cd.kc.longr) grid = std::min(grid, w->scratch_blocks);
+            k<<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pf);
         }
         CUDA_TRY(ctx, cudaGetLastError());
         ++launches;
     }
     // ---- fast kernel only: near-threshold pairs re-decided by the bit-exact scalar kernel -------
     if (mode == 0 && fast32) {
-        for (int kh = 1; kh <= MAX_KH_SCALAR; ++kh) {
+        for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (w->resc_cap[kh] == 0) continue;
-            KernelF32 k = lookup_f32s_f0(kh);
+            KernelF32 k = kh ? lookup_f32s_f0(kh) : lookup_f32_long(2);
             pf.tasks = w->d_guard + w->resc_off[kh];
             pf.ntasks_ptr = w->d_ints + INTS_GUARD + kh;
             pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
             // the exact kernel never takes the guard branch (FAST = false)
-            k<<<grid_for((const void *)k, std::min<int64_t>(w->resc_cap[kh], 4096)), WARPS_PER_BLOCK * 32, 0, st>>>(pf);
+            int grid = grid_for((const void *)k, std::min<int64_t>(w->resc_cap[kh], 4096));
+            if (!kh) grid = std::min(grid, w->scratch_blocks);
+            k<<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pf);
             CUDA_TRY(ctx, cudaGetLastError());
             ++launches;
         }
@@ -451,13 +471,15 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev[1], st));
     // ---- FP64 rescue (IntelPairHmmCSource.cpp:73-75) --------------------------------------------
     if (mode == 0) {
-        for (int kh = 1; kh <= MAX_KH_SCALAR; ++kh) {
+        for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (w->resc_cap[kh] == 0) continue;
-            KernelF64 k = lookup_f64(kh, fast64);
+            KernelF64 k = kh ? lookup_f64(kh, fast64) : lookup_f64_long(fast64);
             pd.tasks = w->d_resc + w->resc_off[kh];
             pd.ntasks_ptr = w->d_ints + INTS_RESC + kh;
             pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
-            k<<<grid_for((const void *)k, w->resc_cap[kh]), WARPS_PER_BLOCK * 32, 0, st>>>(pd);
+            int grid = grid_for((const void *)k, w->resc_cap[kh]);
+            if (!kh) grid = std::min(grid, w->scratch_blocks);
+            k<<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pd);
             CUDA_TRY(ctx, cudaGetLastError());
             ++launches;
         }

@@ -51,6 +51,7 @@ struct Plan {
     int64_t pool_lo = 0, pool_hi = 0;    // referenced byte range of the read pools
     int64_t resc_cap[MAX_KH_SCALAR + 1]; // pairs whose read falls in each scalar class
     int max_rslen = 0, max_haplen = 0;
+    int long_max_cols = 0;               // longest run handed to a multi-pass kernel (0 = none)
 };
 
 // Chooses the kernel class for a read length; returns false when no single-pass class fits.
@@ -73,6 +74,8 @@ KernelF64 lookup_f64_f0(int kh);
 KernelF64 lookup_f64_f1(int kh);
 KernelF32 lookup_f32(const KClass &kc, bool fast);
 KernelF64 lookup_f64(int kh, bool fast);
+KernelF32 lookup_f32_long(int which);
+KernelF64 lookup_f64_long(bool fast);
 cudaError_t launch_pipe_bench(int which, float *out, int grid, int iters, cudaStream_t st,
                               double *ops_per_thread);
 

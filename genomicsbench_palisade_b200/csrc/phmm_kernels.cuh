@@ -170,7 +170,7 @@ __device__ __forceinline__ void emit_result(const KernelParams<double> &P, doubl
 // ------------------------------------------------------------------------------------------
 // The forward kernel.  Persistent warps pull tasks from a device-side queue.
 // ------------------------------------------------------------------------------------------
-template <typename T, int VL, int KH, int LANES, bool FAST, int MINB>
+template <typename T, int VL, int KH, int LANES, bool FAST, bool LONG, int MINB>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
 phmm_forward_kernel(const KernelParams<T> P)
 {
@@ -209,17 +209,30 @@ phmm_forward_kernel(const KernelParams<T> P)
             R = rr.len; roff = rr.off; out_base = rr.out_base;
         }
 
+        // Multi-pass (LONG) kernels cut the read into blocks of NV * KH rows; block `pass` reads
+        // the previous block's bottom row from spill_in and leaves its own in spill_out.
+        const int npass = LONG ? (R + NV * KH) / (NV * KH) : 1;
+        T *spill_in = nullptr, *spill_out = nullptr;
+        int64_t spill_cols = 0;
+        if (LONG) {
+            const int64_t wslot = (int64_t)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+            spill_cols = P.scratch_stride / 6;
+            spill_in = P.scratch + wslot * P.scratch_stride;
+            spill_out = spill_in + 3 * spill_cols;
+        }
+      for (int pass = 0; pass < npass; ++pass) {
+        const bool final_pass = (pass == npass - 1);
         // ---- per-row constants (initializeVectors :83-128, stripeINITIALIZATION :151-158) ----
         V pMM[KH], pG[KH], pMX[KH], pXX[KH], pMY[KH], em[KH], ex[KH];
         V pYY0;                       // pYY of row 0 of each virtual lane (see dummy rows below)
         uint32_t rbits[VL], dmask[VL];
-        const int nd = NV * KH - R;   // dummy rows on top; >= 1 by construction of the classes
+        const int nd = npass * NV * KH - R;   // dummy rows on top of block 0; always >= 1
 #pragma unroll
         for (int c = 0; c < VL; ++c) {
             rbits[c] = 0; dmask[c] = 0;
 #pragma unroll
             for (int p = 0; p < KH; ++p) {
-                const int r = (gl * VL + c) * KH + p - nd;    // 0-based read position
+                const int r = pass * NV * KH + (gl * VL + c) * KH + p - nd;    // 0-based read position
                 T mm = zero, g = zero, mx = zero, xx = zero, my = zero, e1 = zero, e3 = zero, yy = zero;
                 if (r >= 0) {
                     const int _q = P.q[roff + r] & 127, _i = P.i[roff + r] & 127;
@@ -286,6 +299,10 @@ phmm_forward_kernel(const KernelParams<T> P)
 
         const int vpos = gl * VL;                   // first virtual lane of this thread
         uint32_t hb_next = 0, hrep_prev = 0;
+        T sp_m = zero, sp_x = zero, sp_y = zero;
+        if (LONG && pass > 0 && gl == 0) {
+            sp_m = __ldcg(spill_in); sp_x = __ldcg(spill_in + spill_cols); sp_y = __ldcg(spill_in + 2 * spill_cols);
+        }
 
         for (int cb = 0, ch = 0; cb < s_end; cb += STREAM_CHUNK, ++ch) {
             cp_async_wait_all();
@@ -311,7 +328,16 @@ phmm_forward_kernel(const KernelParams<T> P)
                         O::set(U1m, 1, O::get(M[KH - 1], 0)); O::set(U1x, 1, O::get(X[KH - 1], 0));
                         O::set(U1y, 1, O::get(Y[KH - 1], 0));
                     }
-                    O::set(U1m, 0, rm); O::set(U1x, 0, rx); O::set(U1y, 0, ry);
+                    if (LONG && pass > 0 && gl == 0) {     // first row of a later block: "up" is the
+                        O::set(U1m, 0, sp_m); O::set(U1x, 0, sp_x); O::set(U1y, 0, sp_y);   // block above
+                        const int ncol = s + 1 - a;
+                        if (ncol < ncols) {
+                            sp_m = __ldcg(spill_in + ncol); sp_x = __ldcg(spill_in + spill_cols + ncol);
+                            sp_y = __ldcg(spill_in + 2 * spill_cols + ncol);
+                        }
+                    } else {
+                        O::set(U1m, 0, rm); O::set(U1x, 0, rx); O::set(U1y, 0, ry);
+                    }
                 }
                 // -- haplotype code of this step's column (prefetched) and of the next one
                 const uint32_t hb = hb_next;
@@ -364,7 +390,7 @@ phmm_forward_kernel(const KernelParams<T> P)
                             const int col = s - a - (vpos + c);
                             if (col >= 0 && col < ncols) {          // separator after haplotype jh[c]
                                 if (c == VL - 1) {
-                                    if (last_lane && active) {
+                                    if (last_lane && active && final_pass) {
                                         const T res = S::add(sumM, sumX);   // :342
                                         emit_result<FAST>(P, res, out_base + out0 + jh[c],
                                                           stream_off + hapstart, col - hapstart,
@@ -386,8 +412,21 @@ phmm_forward_kernel(const KernelParams<T> P)
                 // -- last-row sums (:328,:331): two separate sequential sums in column order
                 sumM = S::add(sumM, O::get(M[KH - 1], VL - 1));
                 sumX = S::add(sumX, O::get(X[KH - 1], VL - 1));
+                if (LONG && !final_pass && last_lane) {
+                    const int col = s - a - (NV - 1);
+                    if (col >= 0 && col < ncols) {
+                        spill_out[col] = O::get(M[KH - 1], VL - 1);
+                        spill_out[spill_cols + col] = O::get(X[KH - 1], VL - 1);
+                        spill_out[2 * spill_cols + col] = O::get(Y[KH - 1], VL - 1);
+                    }
+                }
             }
         }
+        if (LONG) {
+            __syncwarp();
+            T *tmp = spill_in; spill_in = spill_out; spill_out = tmp;
+        }
+      }   // pass
     }
 }
 
@@ -402,10 +441,10 @@ struct MinBlocks {
 typedef void (*KernelF32)(const KernelParams<float>);
 typedef void (*KernelF64)(const KernelParams<double>);
 
-template <int VL, int KH, int LANES, bool FAST>
-static KernelF32 f32_kernel() { return phmm_forward_kernel<float, VL, KH, LANES, FAST, MinBlocks<float, VL, KH>::value>; }
-template <int KH, bool FAST>
-static KernelF64 f64_kernel() { return phmm_forward_kernel<double, 1, KH, 32, FAST, MinBlocks<double, 1, KH>::value>; }
+template <int VL, int KH, int LANES, bool FAST, bool LONG = false>
+static KernelF32 f32_kernel() { return phmm_forward_kernel<float, VL, KH, LANES, FAST, LONG, MinBlocks<float, VL, KH>::value>; }
+template <int KH, bool FAST, bool LONG = false>
+static KernelF64 f64_kernel() { return phmm_forward_kernel<double, 1, KH, 32, FAST, LONG, MinBlocks<double, 1, KH>::value>; }
 
 }  // namespace phmm
 #endif

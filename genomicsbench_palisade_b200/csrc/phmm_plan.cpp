@@ -18,15 +18,13 @@ namespace phmm {
 bool choose_class(int rslen, const PlanOptions &opt, KClass *out)
 {
     if (opt.force_kh > 0 && opt.force_lanes > 0) {
-        KClass kc{opt.force_kh, opt.force_lanes, (opt.packed && opt.precision != 2) ? 2 : 1};
-        if (kc.capacity() < rslen) return false;
-        *out = kc;
-        return true;
+        KClass kc{opt.force_kh, opt.force_lanes, (opt.packed && opt.precision != 2) ? 2 : 1, 0};
+        if (kc.capacity() >= rslen) { *out = kc; return true; }
     }
     bool found = false;
     double best = 0;
     auto consider = [&](int kh, int lanes, int vl) {
-        KClass kc{kh, lanes, vl};
+        KClass kc{kh, lanes, vl, 0};
         if (kc.capacity() < rslen) return;
         // issue slots per column ~ lanes x (tile rows + fixed per-step work); the wavefront
         // fill/drain (vl * lanes - 1 steps per run) is a second-order term added per task
@@ -39,6 +37,13 @@ bool choose_class(int rslen, const PlanOptions &opt, KClass *out)
         for (int kh = 1; kh <= 4; ++kh) consider(kh, 32, 2);
     } else {
         for (int kh = 1; kh <= MAX_KH_SCALAR; ++kh) consider(kh, 32, 1);
+    }
+    if (!found) {
+        // longer than every single-pass class: multi-pass kernel
+        if (opt.precision == 2) *out = KClass{LONG_KH_F64, 32, 1, 1};
+        else if (opt.packed) *out = KClass{LONG_KH_F32, 32, 2, 1};
+        else *out = KClass{LONG_KH_F32S, 32, 1, 1};
+        found = true;
     }
     return found;
 }
@@ -125,7 +130,8 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
     struct ClassKey { int kh, lanes, vl; };
     auto class_index = [&](const KClass &kc) -> int {
         for (size_t k = 0; k < P.classes.size(); ++k)
-            if (P.classes[k].kc.kh == kc.kh && P.classes[k].kc.lanes == kc.lanes && P.classes[k].kc.vl == kc.vl)
+            if (P.classes[k].kc.kh == kc.kh && P.classes[k].kc.lanes == kc.lanes && P.classes[k].kc.vl == kc.vl &&
+                P.classes[k].kc.longr == kc.longr)
                 return (int)k;
         ClassPlan cp;
         cp.kc = kc;
@@ -214,6 +220,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
                         t.read[j] = (j < g && i + j < rl.size()) ? rl[i + j] : -1;
                     t.pad = 0;
                     P.classes[c].tasks.push_back(t);
+                    if (P.classes[c].kc.longr) P.long_max_cols = std::max(P.long_max_cols, t.ncols);
                 }
             }
             k = k1;

@@ -50,9 +50,14 @@ struct Task {
 //   vl    virtual lanes per thread: 2 = FP32 packed f32x2 (Blackwell FMUL2/FFMA2), 1 = scalar
 // capacity = vl * kh * lanes - 1 read rows (row 0 of the first virtual lane is always a dummy
 // row that re-creates the DP's row-0 boundary, so no per-step select is needed there).
+//   longr 1 = multi-pass kernel for reads longer than any single-pass class: the read is cut
+//         into blocks of vl * kh * lanes rows, processed one block per pass over the same columns;
+//         the bottom row of a block travels to the next pass through an HBM scratch row
+//         (the reference does the same one level down with its shiftOut arrays,
+//         avx-pairhmm-template.h:224,265-297).
 struct KClass {
-    int kh, lanes, vl;
-    int capacity() const { return vl * kh * lanes - 1; }
+    int kh, lanes, vl, longr;
+    int capacity() const { return longr ? 0x7fffffff : vl * kh * lanes - 1; }
     int group() const { return 32 / lanes; }
 };
 
@@ -60,6 +65,7 @@ static const int STREAM_CHUNK = 512;          // haplotype-stream bytes staged p
 static const int STREAM_RING = 2048;          // per-warp shared-memory ring (4 chunks)
 static const int STREAM_SLACK = 2 * STREAM_CHUNK + 128;   // readable bytes past the last column
 static const int WARPS_PER_BLOCK = 4;
+static const int LONG_KH_F32 = 4, LONG_KH_F32S = 8, LONG_KH_F64 = 4;   // register tiles of the multi-pass kernels
 static const int MAX_KH_SCALAR = 8;           // scalar single-pass classes: 32 lanes x kh rows, kh <= 8
 
 template <typename T>
@@ -86,6 +92,8 @@ struct KernelParams {
     float guard_lo, guard_hi;            // fast kernel: sums in [lo, hi) go to the exact kernel
     Task *guard;                         // guard-band list (fast kernel only)
     int32_t *guard_count;
+    T *scratch;                          // multi-pass kernels: per-warp boundary rows
+    int64_t scratch_stride;              // elements of T per warp (2 buffers x 3 arrays x columns)
 };
 
 }  // namespace phmm

@@ -1,0 +1,213 @@
+"""GPU (-m gpu): libphmm_cuda through its C ABI against the CPU oracle and the golden vectors.
+
+Bars (BASELINE.json north_star): FP64-rescue set identical; FP32-path log10 within 1e-4 relative;
+rescued pairs within 1e-9 relative.  The bit-exact kernels are held to more: raw FP32 and FP64
+sums bit-identical to the reference's AVX code."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle
+from conftest import GOLDEN_NAMES, load_golden, max_rel, same_or_close
+from genomicsbench_palisade_b200 import phmm, synth
+from genomicsbench_palisade_b200.batches import from_lists
+
+pytestmark = pytest.mark.gpu
+
+RTOL_FP32 = 1e-4      # north_star: <= 1e-4 relative on the FP32 path
+RTOL_FP64 = 1e-9      # north_star: <= 1e-9 relative on FP64-rescued pairs
+
+
+def run(fb, **kw):
+    eng = phmm.PairHMM(**kw)
+    w = eng.workload(fb)
+    st = w.run()
+    res = w.results(raw=True)
+    w.close()
+    eng.close()
+    return res, st
+
+
+def check(res, ref_out, ref_raw32, ref_raw64, ref_resc, bit_exact32, bit_exact64):
+    out, raw32, raw64, resc = res
+    assert np.array_equal(resc, ref_resc), "FP64-rescue set differs"
+    r = ref_resc.astype(bool)
+    assert same_or_close(out[~r], ref_out[~r], RTOL_FP32), max_rel(out[~r], ref_out[~r])
+    assert same_or_close(out[r], ref_out[r], RTOL_FP64), max_rel(out[r], ref_out[r])
+    if bit_exact32:
+        assert np.array_equal(raw32.view(np.uint32), ref_raw32.view(np.uint32))
+    if bit_exact64:
+        assert np.array_equal(raw64[r].view(np.uint64), ref_raw64[r].view(np.uint64))
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+@pytest.mark.parametrize("variant", ["packed", "scalar", "fast", "fast64"])
+def test_golden_vectors(name, variant):
+    fb, g = load_golden(name)
+    kw = {"packed": dict(), "scalar": dict(packed=False), "fast": dict(fast=True), "fast64": dict(fast64=True)}[variant]
+    res, _ = run(fb, **kw)
+    check(res, g["out"], g["raw32"], g["raw64"], g["rescued"], variant in ("packed", "scalar", "fast64"),
+          variant != "fast64")
+
+
+def test_known_answer_through_the_legacy_symbols():
+    # PairHmmUnitTest.java:42-49,55 through the reference's own entry points
+    lib = phmm.load_library()
+    lib["_Z11initPairHMMv"]()
+    bufs = [C.create_string_buffer(b, 4) for b in (b"ACGT", b"++++", b"++++", b"++++", b"++++", b"ACGT")]
+    tc = phmm.CTestcase(4, 4, *[C.cast(b, C.c_void_p) for b in (bufs[1], bufs[2], bufs[3], bufs[4], bufs[5], bufs[0])])
+    out = C.c_double()
+    lib["_Z22computelikelihoodsbothP8testcasePdi"](C.byref(tc), C.byref(out), C.c_int(1))
+    assert abs(out.value - (-6.022797e-01)) < 1e-5
+    f = C.c_float()
+    lib["_Z23computelikelihoodsfloatP8testcasePf"](C.byref(tc), C.byref(f))
+    assert abs(f.value - (-6.022797e-01)) < 1e-5
+    d = C.c_double()
+    lib["_Z24computelikelihoodsdoubleP8testcasePd"](C.byref(tc), C.byref(d))
+    assert abs(d.value - (-6.022776589e-01)) < 1e-9
+
+
+@pytest.mark.parametrize("precision", [phmm.FLOAT_ONLY, phmm.DOUBLE_ONLY])
+def test_single_precision_modes(precision):
+    fb, g = load_golden("c1_small")
+    eng = phmm.PairHMM(precision=precision)
+    out = eng.compute(fb)
+    eng.close()
+    want = g["out_f32only"] if precision == phmm.FLOAT_ONLY else g["out_f64only"]
+    assert same_or_close(out, want, RTOL_FP32 if precision == phmm.FLOAT_ONLY else RTOL_FP64)
+
+
+def test_host_entry_points_agree():
+    fb, g = load_golden("c2_large")
+    eng = phmm.PairHMM()
+    a = eng.compute(fb)                 # phmm_compute_flat
+    b = eng.compute_pairs(fb)           # computelikelihoodsboth's testcase[] argument list
+    # phmm_compute_batches: the driver's Batch structs
+    keep, batches = [], []
+    brs, bhs, bos = fb.batch_read_start, fb.batch_hap_start, fb.batch_out_start
+    results = np.zeros(fb.n_pairs, np.float64)
+
+    class CRead(C.Structure):
+        _fields_ = [("length", C.c_int), ("bases", C.c_void_p), ("q", C.c_void_p), ("i", C.c_void_p),
+                    ("d", C.c_void_p), ("c", C.c_void_p)]
+
+    class CHap(C.Structure):
+        _fields_ = [("length", C.c_int), ("bases", C.c_void_p)]
+
+    class CBatch(C.Structure):
+        _fields_ = [("num_reads", C.c_int), ("num_haps", C.c_int), ("reads", C.c_void_p), ("haps", C.c_void_p),
+                    ("results", C.c_void_p)]
+
+    arr = (CBatch * fb.n_batches)()
+    for k in range(fb.n_batches):
+        nr, nh = int(fb.batch_num_reads[k]), int(fb.batch_num_haps[k])
+        reads = (CRead * nr)()
+        for j in range(nr):
+            o, n = int(fb.read_off[brs[k] + j]), int(fb.read_len[brs[k] + j])
+            reads[j] = CRead(n, *[getattr(fb, f).ctypes.data + o for f in ("rs", "q", "i", "d", "c")])
+        haps = (CHap * nh)()
+        for j in range(nh):
+            haps[j] = CHap(int(fb.hap_len[bhs[k] + j]), fb.hap.ctypes.data + int(fb.hap_off[bhs[k] + j]))
+        keep += [reads, haps]
+        arr[k] = CBatch(nr, nh, C.cast(reads, C.c_void_p), C.cast(haps, C.c_void_p),
+                        results.ctypes.data + 8 * int(bos[k]))
+    eng._check(eng.lib.phmm_compute_batches(eng._h, arr, C.c_int64(fb.n_batches)))
+    eng.close()
+    assert np.array_equal(a, b) and np.array_equal(a, results)
+    assert same_or_close(a, g["out"], RTOL_FP32)
+
+
+def test_random_workloads_against_the_oracle():
+    for fb in (synth.generic(31, 12, (1, 60), (1, 20), (1, 255), (1, 700), q_rng=(6, 45), subst=0.08,
+                             foreign_frac=0.15),
+               synth.c1_small(0.04), synth.c4_stress(800), synth.c5_skewed(4000)):
+        ref = oracle.run_port(fb)
+        for kw, e32 in ((dict(), True), (dict(fast=True, fast64=True), False)):
+            res, _ = run(fb, **kw)
+            check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, e32, e32)
+
+
+def test_every_kernel_class_is_bit_exact():
+    # pin each register-tile height / lane-group width in turn on reads that fit it
+    base = synth.generic(41, 4, (20, 40), (3, 8), (1, 60), (20, 400), q_rng=(6, 45), subst=0.05, foreign_frac=0.2)
+    for packed, lanes_set, khs in ((True, (32,), range(1, 5)), (True, (16, 8), range(1, 7)), (False, (32,), range(1, 9))):
+        for lanes in lanes_set:
+            for kh in khs:
+                cap = (2 if packed else 1) * kh * lanes - 1
+                rng = np.random.default_rng(kh * 100 + lanes)
+                fb = synth.generic(1000 + kh * 100 + lanes, 3, (6, 12), (2, 6), (max(1, cap - 40), cap), (10, 300),
+                                   q_rng=(6, 45), subst=0.05, foreign_frac=0.2)
+                ref = oracle.run_port(fb)
+                res, st = run(fb, packed=packed, force_class=(kh, lanes))
+                assert st["n_classes"] == 1
+                check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, True, True)
+
+
+def test_long_reads_multi_pass():
+    # reads far beyond the largest register tile; haplotypes shorter and longer than the reads
+    fb = synth.generic(51, 3, (3, 6), (2, 5), (256, 1500), (50, 2500), q_rng=(6, 45), subst=0.05, foreign_frac=0.3)
+    ref = oracle.run_port(fb)
+    for kw, exact in ((dict(), True), (dict(packed=False), True), (dict(fast=True), False)):
+        res, _ = run(fb, **kw)
+        check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, exact, True)
+    eng = phmm.PairHMM(precision=phmm.DOUBLE_ONLY)
+    out = eng.compute(fb)
+    eng.close()
+    assert same_or_close(out, oracle.run_port(fb, mode=2).out, RTOL_FP64)
+
+
+def test_fast_kernel_keeps_the_rescue_set_near_the_threshold():
+    # many pairs whose FP32 sum lands around MIN_ACCEPTED = 1e-28f: the fast kernel must send exactly
+    # the reference's set to FP64 (guard band + bit-exact re-decision)
+    fb = synth.generic(61, 40, (30, 30), (6, 6), (100, 150), (150, 300), q_rng=(20, 40), subst=0.15)
+    ref = oracle.run_port(fb)
+    frac = ref.rescued.mean()
+    assert 0.02 < frac < 0.98
+    res, st = run(fb, fast=True)
+    assert np.array_equal(res[3], ref.rescued)
+    near = (ref.raw32 > 0.99e-28) & (ref.raw32 < 1.01e-28)
+    assert st["n_guard"] >= int(near.sum())
+
+
+def test_full_size_properties():
+    """BASELINE config 2 at full size (2 M pairs): size-independent checks instead of the oracle."""
+    fb = synth.c2_large()
+    eng = phmm.PairHMM()
+    w = eng.workload(fb)
+    w.run()
+    out, raw32, raw64, resc = w.results(raw=True)
+    w.run()
+    out2 = w.results()
+    w.close()
+    assert np.array_equal(out, out2)                               # deterministic / idempotent
+    assert np.isfinite(out).all() and (out < 0).all()              # log10 of a probability
+    # scalar and packed kernels are two different programs: identical raw sums
+    eng_s = phmm.PairHMM(packed=False)
+    w = eng_s.workload(fb)
+    w.run()
+    _, raw32_s, raw64_s, resc_s = w.results(raw=True)
+    w.close()
+    eng_s.close()
+    assert np.array_equal(raw32.view(np.uint32), raw32_s.view(np.uint32))
+    assert np.array_equal(raw64.view(np.uint64), raw64_s.view(np.uint64)) and np.array_equal(resc, resc_s)
+    # permuting the haplotypes of every batch permutes the results and nothing else
+    rng = np.random.default_rng(1)
+    bhs, bos = fb.batch_hap_start, fb.batch_out_start
+    perm = np.concatenate([bhs[b] + rng.permutation(int(fb.batch_num_haps[b])) for b in range(fb.n_batches)])
+    fb_p = type(fb)(fb.batch_num_reads, fb.batch_num_haps, fb.read_len, fb.read_off, fb.rs, fb.q, fb.i, fb.d,
+                    fb.c, fb.hap_len[perm], fb.hap_off[perm], fb.hap)
+    out_p = eng.compute(fb_p)
+    eng.close()
+    idx = []
+    for b in range(fb.n_batches):
+        nr, nh = int(fb.batch_num_reads[b]), int(fb.batch_num_haps[b])
+        local = perm[bhs[b]:bhs[b] + nh] - bhs[b]
+        idx.append((bos[b] + np.arange(nr)[:, None] * nh + local[None, :]).ravel())
+    assert np.array_equal(out_p, out[np.concatenate(idx)])
+    # a seeded sample against the oracle
+    sub = fb.select_batches(np.array([0]))
+    ref = oracle.run_port(sub)
+    n = sub.n_pairs
+    assert np.array_equal(raw32[:n].view(np.uint32), ref.raw32.view(np.uint32))
+    assert np.array_equal(resc[:n], ref.rescued)

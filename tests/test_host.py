@@ -1,0 +1,162 @@
+"""CPU: host-side logic of libphmm_cuda (no device): exports, tables, planner, parser, scheduler."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import oracle
+from conftest import ROOT, load_golden
+from genomicsbench_palisade_b200 import phmm, synth
+from genomicsbench_palisade_b200.batches import FlatBatches, from_lists
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "phmm_cuda.h")).read()
+    body = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(phmm_[a-z0-9_]+)\s*\(", body))
+    assert {"phmm_create", "phmm_compute_pairs", "phmm_compute_flat", "phmm_workload_run"} <= declared
+    lib = phmm.load_library()
+    for name in sorted(declared):
+        assert hasattr(lib, name), "libphmm_cuda.so does not export " + name
+    assert declared == set(phmm.EXPORTS)
+    # the reference's own C++-linkage symbols (IntelPairHmmCSource.cpp:29,61,89,103; pairhmm_common.cc:3)
+    for name in phmm.LEGACY_EXPORTS:
+        assert hasattr(lib, name), name
+    assert lib.phmm_abi_version() == 1
+
+
+def test_no_cpu_fallback_without_a_device():
+    lib = phmm.load_library()
+    if lib.phmm_device_count() > 0:
+        pytest.skip("a GPU is visible")
+    with pytest.raises(phmm.PhmmError) as e:
+        phmm.PairHMM()
+    assert e.value.code == 4 and "no CPU fallback" in str(e.value)
+
+
+def test_product_never_touches_the_oracle():
+    pkg = os.path.join(ROOT, "genomicsbench_palisade_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")) or f == "Makefile":
+                txt = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "import oracle" not in txt and "liboracle" not in txt and "libphmm_ref" not in txt, f
+                assert "oracle/" not in txt, f
+
+
+def test_uploaded_tables_equal_the_oracle_tables():
+    t, o = phmm.get_tables(), oracle.port_tables()
+    assert np.array_equal(t["ph2pr_f"].view(np.uint32), o["ph2pr_f"].view(np.uint32))
+    assert np.array_equal(t["ph2pr_d"].view(np.uint64), o["ph2pr_d"].view(np.uint64))
+    assert np.array_equal(t["mm_f"].view(np.uint32), o["mm_f"][:8256].view(np.uint32))
+    assert np.array_equal(t["mm_d"].view(np.uint64), o["mm_d"][:8256].view(np.uint64))
+    for k in ("init_f", "log10_init_f", "init_d", "log10_init_d"):
+        assert t[k] == o[k], k
+
+
+@pytest.mark.parametrize("packed,precision", [(1, 0), (0, 0), (1, 2)])
+def test_plan_covers_every_pair_exactly_once(packed, precision):
+    for fb in (synth.edge_cases(), synth.c1_small(0.03), synth.c2_large(60000), synth.c4_stress(800),
+               synth.c5_skewed(6000)):
+        s = phmm.plan_summary(fb, precision=precision, packed=packed)
+        assert s["pairs"] == fb.n_pairs and s["cells"] == fb.n_cells
+        assert (s["cover"] == 1).all()
+        for kh, lanes, vl, ntasks in s["classes"]:
+            assert lanes in (8, 16, 32) and vl == (2 if packed and precision != 2 else 1) and ntasks > 0
+    s = phmm.plan_summary(synth.c2_large(60000), seg_cols=700)
+    assert (s["cover"] == 1).all()
+
+
+def test_plan_rejects_bad_input():
+    with pytest.raises(phmm.PhmmError) as e:
+        phmm.plan_summary(from_lists([([(b"", b"", b"", b"", b"")], [b"ACGT"])]))
+    assert e.value.code == 2                      # PHMM_ERR_EMPTY_SEQ: rslen == 0
+    with pytest.raises(phmm.PhmmError) as e:
+        phmm.plan_summary(from_lists([([(b"A", b"5", b"5", b"5", b"5")], [b""])]))
+    assert e.value.code == 2                      # haplen == 0: the reference divides by it
+    empty = from_lists([])
+    s = phmm.plan_summary(empty)
+    assert s["pairs"] == 0 and s["tasks"] == 0
+    s = phmm.plan_summary(from_lists([([(b"ACGT", b"5555", b"5555", b"5555", b"5555")], [])]))
+    assert s["pairs"] == 0
+
+
+def test_parser_matches_the_reference_driver_semantics():
+    fb = synth.generic(5, 7, (1, 9), (1, 5), (1, 80), (1, 120), q_rng=(6, 45), foreign_frac=0.2)
+    txt = fb.to_text()
+    a = phmm.parse_text(txt)
+    b = FlatBatches.from_text(txt)                   # python mirror of read_batch
+    for k in ("batch_num_reads", "batch_num_haps", "read_len", "hap_len", "rs", "q", "i", "d", "c", "hap"):
+        assert np.array_equal(getattr(a, k), getattr(b, k)), k
+        assert np.array_equal(getattr(a, k), getattr(fb, k)), k
+    # normalize(): max(floor, byte - 33) with floor 6 for q and 0 for i/d/c (_orig.cpp:88-92,120-123)
+    t = phmm.parse_text(b"1 1\nACGT !!+5 !!!+ \"#$% ++++\nAC\n")
+    assert t.q.tolist() == [6, 6, 10, 20] and t.i.tolist() == [0, 0, 0, 10] and t.d.tolist() == [1, 2, 3, 4]
+    # any whitespace separates tokens, trailing whitespace ends the file (operator>> + ws)
+    t2 = phmm.parse_text(b"  1\t1 ACGT\n!!+5\r\n!!!+ \"#$% ++++ AC \n\n")
+    assert np.array_equal(t2.q, t.q) and t2.hap.tobytes() == b"AC"
+    assert phmm.parse_text(b"").n_batches == 0
+    for bad in (b"1 1\nACGT !!! !!!! !!!! !!!!\nAC\n", b"1 1\nACGT !!!! !!!! !!!!\n", b"x 1\n", b"2 1\nA ! ! ! !\nAC\n"):
+        with pytest.raises(phmm.PhmmError) as e:
+            phmm.parse_text(bad)
+        assert e.value.code == 6
+
+
+def test_lpt_partition():
+    rng = np.random.default_rng(3)
+    cost = rng.integers(1, 10**9, 500)
+    for parts in (1, 2, 4, 8):
+        owner = phmm.partition_lpt(cost, parts)
+        assert owner.min() >= 0 and owner.max() < parts
+        load = np.bincount(owner, weights=cost, minlength=parts)
+        assert load.max() - load.min() <= cost.max()          # LPT bound
+        assert load.max() / load.mean() < 1.01                # < 1 % imbalance
+        assert np.array_equal(owner, phmm.partition_lpt(cost, parts))   # deterministic across ranks
+
+
+def test_batches_helpers():
+    fb, g = load_golden("c1_small")
+    rsl, hpl, _, _ = fb.pairs()
+    assert int((rsl.astype(np.int64) * hpl).sum()) == fb.n_cells == int(fb.batch_cells.sum())
+    sub, idx = fb.select_reads(fb.read_len <= 120)
+    r = oracle.run_port(sub)
+    assert np.array_equal(r.out, g["out"][idx])
+    half = fb.select_batches(np.arange(0, fb.n_batches, 2))
+    r2 = oracle.run_port(half)
+    bos = fb.batch_out_start
+    want = np.concatenate([g["out"][bos[b]:bos[b + 1]] for b in range(0, fb.n_batches, 2)])
+    assert np.array_equal(r2.out, want)
+
+
+def test_two_rank_sharding_gloo(tmp_path):
+    """N > 1 path on CPU: two gloo ranks build the same LPT map, take disjoint batch sets that
+    cover the workload, and the all-reduced cell counts add up (bench.py's sharding logic)."""
+    script = tmp_path / "rank.py"
+    script.write_text(
+        "import os, sys, json\n"
+        "sys.path.insert(0, %r)\n"
+        "import numpy as np, torch, torch.distributed as dist\n"
+        "import bench\n"
+        "dist.init_process_group('gloo')\n"
+        "rank, world = dist.get_rank(), dist.get_world_size()\n"
+        "fb, mine = bench.make_shard('tiny', rank, world)\n"
+        "t = torch.tensor([mine.n_cells, mine.n_pairs, mine.n_batches], dtype=torch.int64)\n"
+        "dist.all_reduce(t)\n"
+        "own = torch.zeros(fb.n_batches, dtype=torch.int64)\n"
+        "own[bench.my_batches(fb, rank, world)] = 1\n"
+        "dist.all_reduce(own)\n"
+        "ok = bool((own == 1).all()) and int(t[0]) == fb.n_cells and int(t[1]) == fb.n_pairs\n"
+        "if rank == 0: print(json.dumps({'ok': ok, 'cells': int(t[0]), 'world': world}))\n"
+        "dist.destroy_process_group()\n" % ROOT)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29517", str(script)],
+                         capture_output=True, text=True, timeout=300, env=env)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = [l for l in out.stdout.splitlines() if l.startswith("{")][-1]
+    import json
+    res = json.loads(line)
+    assert res["ok"] and res["world"] == 2
