@@ -283,6 +283,9 @@ phmm_forward_kernel(const KernelParams<T> P)
             }
         }
         V U1m = O::splat(zero), U1x = O::splat(zero), U1y = O::splat(zero);
+        // a later block whose block above is nothing but dummy rows sits directly under DP row 0:
+        // its diagonal neighbour at the first column is Y[0][0] = INITIAL_CONSTANT / haplen
+        if (LONG && pass > 0 && gl == 0 && nd >= pass * NV * KH) O::set(U1y, 0, initY[0]);
         V U2m, U2x, U2y;
         T sumM = zero, sumX = zero;
         int hapstart = 0;
