@@ -30,7 +30,7 @@ struct phmm_ctx {
     double *d_ph2pr_d = nullptr, *d_mm_d = nullptr;
     float *d_bench = nullptr;
     // options
-    int precision = 0, fp32_fast = 0, fp64_fast = 0, seg_cols = 0, packed = 1;
+    int precision = 0, fp32_fast = 0, fp64_fast = 0, seg_cols = 0;
     int force_kh = 0, force_lanes = 0;
     std::string error;
     std::mutex mu;     // the legacy symbols may be entered from several OpenMP threads
@@ -105,12 +105,11 @@ int dev_alloc(phmm_ctx *ctx, T **p, size_t n)
 namespace phmm {
 KernelF32 lookup_f32(const KClass &kc, bool fast)
 {
-    if (kc.longr) return lookup_f32_long(kc.vl == 2 ? (fast ? 1 : 0) : (fast ? 3 : 2));
-    if (kc.vl == 1) return kc.lanes == 32 ? (fast ? lookup_f32s_f1(kc.kh) : lookup_f32s_f0(kc.kh)) : nullptr;
+    if (kc.vl != 2) return nullptr;
+    if (kc.longr) return lookup_f32_long(fast);
     switch (kc.lanes) {
-    case 32: return fast ? lookup_f32p_l32_f1(kc.kh) : lookup_f32p_l32_f0(kc.kh);
-    case 16: return fast ? lookup_f32p_l16_f1(kc.kh) : lookup_f32p_l16_f0(kc.kh);
-    case 8:  return fast ? lookup_f32p_l8_f1(kc.kh) : lookup_f32p_l8_f0(kc.kh);
+    case 32: return fast ? lookup_f32_l32_f1(kc.kh) : lookup_f32_l32_f0(kc.kh);
+    case 16: return fast ? lookup_f32_l16_f1(kc.kh) : lookup_f32_l16_f0(kc.kh);
     default: return nullptr;
     }
 }
@@ -205,7 +204,6 @@ extern "C" int phmm_set_option(phmm_ctx *ctx, int option, int64_t value)
     case PHMM_OPT_FP32_KERNEL: if (value < 0 || value > 1) break; ctx->fp32_fast = (int)value; return PHMM_OK;
     case PHMM_OPT_FP64_KERNEL: if (value < 0 || value > 1) break; ctx->fp64_fast = (int)value; return PHMM_OK;
     case PHMM_OPT_SEG_COLS:    if (value < 0 || value > (1 << 24)) break; ctx->seg_cols = (int)value; return PHMM_OK;
-    case PHMM_OPT_PACKED:      if (value < 0 || value > 1) break; ctx->packed = (int)value; return PHMM_OK;
     case PHMM_OPT_FORCE_CLASS: ctx->force_kh = (int)(value >> 8); ctx->force_lanes = (int)(value & 255); return PHMM_OK;
     default: break;
     }
@@ -221,7 +219,6 @@ extern "C" int64_t phmm_get_option(const phmm_ctx *ctx, int option)
     case PHMM_OPT_FP32_KERNEL: return ctx->fp32_fast;
     case PHMM_OPT_FP64_KERNEL: return ctx->fp64_fast;
     case PHMM_OPT_SEG_COLS: return ctx->seg_cols;
-    case PHMM_OPT_PACKED: return ctx->packed;
     case PHMM_OPT_FORCE_CLASS: return ((int64_t)ctx->force_kh << 8) | ctx->force_lanes;
     default: return -1;
     }
@@ -247,7 +244,6 @@ static PlanOptions plan_options(const phmm_ctx *ctx)
 {
     PlanOptions o;
     o.precision = ctx->precision;
-    o.packed = ctx->packed;
     o.seg_cols = ctx->seg_cols;
     o.force_kh = ctx->force_kh;
     o.force_lanes = ctx->force_lanes;
@@ -325,7 +321,7 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
     }
     if (P.long_max_cols > 0) {
         // long reads may also come back as single-haplotype rescue / guard tasks
-        const int64_t cols = std::max<int64_t>(P.long_max_cols, P.max_haplen + 1) + 64;
+        const int64_t cols = std::max<int64_t>(P.long_max_cols, P.max_haplen + SEP_COLS) + 64;
         w->scratch_stride = 6 * cols;
         w->scratch_blocks = ctx->sm_count * 2;
         WL_ALLOC(w->d_scratch, w->scratch_stride * w->scratch_blocks * WARPS_PER_BLOCK);
@@ -412,17 +408,23 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
     pd.init_const = t.init_d; pd.log10_init = t.log10_init_d;
     pd.out = w->d_out; pd.raw32 = w->d_raw32; pd.raw64 = w->d_raw64; pd.rescued = w->d_rescued;
     pd.mode = mode;
-    pf.scratch = reinterpret_cast<float *>(w->d_scratch); pf.scratch_stride = w->scratch_stride;
+    pf.scratch = reinterpret_cast<float *>(w->d_scratch); pf.scratch_stride = 2 * w->scratch_stride;   // in floats
     pd.scratch = w->d_scratch; pd.scratch_stride = w->scratch_stride;
 
-    auto grid_for = [&](const void *kernel, int64_t ntasks) -> int {
+    // dynamic shared memory (emission table + stream ring + run table per warp) and a grid that
+    // fills the device once: the kernels are persistent, warps pull tasks from the queue
+    auto prepare = [&](const void *kernel, int kh, int64_t ntasks, bool longr, int *grid, int *smem) -> bool {
+        *smem = WARPS_PER_BLOCK * smem_per_warp(kh);
+        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, *smem) != cudaSuccess) return false;
         int nb = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, WARPS_PER_BLOCK * 32, 0) != cudaSuccess || nb < 1) nb = 1;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, WARPS_PER_BLOCK * 32, *smem) != cudaSuccess || nb < 1) nb = 1;
         const int64_t full = (int64_t)nb * ctx->sm_count;
         const int64_t want = (ntasks + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
-        return (int)std::max<int64_t>(1, std::min(full, want));
+        *grid = (int)std::max<int64_t>(1, std::min(full, want));
+        if (longr) *grid = std::min(*grid, w->scratch_blocks);
+        return true;
     };
-    int counter_slot = 0;
+    int counter_slot = 0, grid = 0, smem = 0;
 
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev[0], st));
     // ---- main pass over the planned tasks ---------------------------------------------------
@@ -436,34 +438,31 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
             pd.tasks = w->d_tasks + cd.task_off;
             pd.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
             pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
-            int grid = grid_for((const void *)k, cd.ntasks);
-            if (cd.kc.longr) grid = std::min(grid, w->scratch_blocks);
-            k<<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pd);
+            if (!prepare((const void *)k, cd.kc.kh, cd.ntasks, cd.kc.longr, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, st>>>(pd);
         } else {
             KernelF32 k = lookup_f32(cd.kc, fast32);
             if (!k) { ctx->error = "no FP32 kernel for class"; return PHMM_ERR_ARG; }
             pf.tasks = w->d_tasks + cd.task_off;
             pf.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
             pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
-            int grid = grid_for((const void *)k, cd.ntasks);
-            if (cd.kc.longr) grid = std::min(grid, w->scratch_blocks);
-            k<<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pf);
+            if (!prepare((const void *)k, cd.kc.kh, cd.ntasks, cd.kc.longr, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, st>>>(pf);
         }
         CUDA_TRY(ctx, cudaGetLastError());
         ++launches;
     }
-    // ---- fast kernel only: near-threshold pairs re-decided by the bit-exact scalar kernel -------
+    // ---- fast kernel only: near-threshold pairs re-decided by the bit-exact kernel ---------------
     if (mode == 0 && fast32) {
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (w->resc_cap[kh] == 0) continue;
-            KernelF32 k = kh ? lookup_f32s_f0(kh) : lookup_f32_long(2);
+            KernelF32 k = kh ? lookup_f32_l32_f0(kh) : lookup_f32_long(false);
             pf.tasks = w->d_guard + w->resc_off[kh];
             pf.ntasks_ptr = w->d_ints + INTS_GUARD + kh;
             pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
             // the exact kernel never takes the guard branch (FAST = false)
-            int grid = grid_for((const void *)k, std::min<int64_t>(w->resc_cap[kh], 4096));
-            if (!kh) grid = std::min(grid, w->scratch_blocks);
-            k<<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pf);
+            if (!prepare((const void *)k, kh ? kh : LONG_KH, std::min<int64_t>(w->resc_cap[kh], 4096), kh == 0, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, st>>>(pf);
             CUDA_TRY(ctx, cudaGetLastError());
             ++launches;
         }
@@ -477,9 +476,8 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
             pd.tasks = w->d_resc + w->resc_off[kh];
             pd.ntasks_ptr = w->d_ints + INTS_RESC + kh;
             pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
-            int grid = grid_for((const void *)k, w->resc_cap[kh]);
-            if (!kh) grid = std::min(grid, w->scratch_blocks);
-            k<<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pd);
+            if (!prepare((const void *)k, kh ? kh : LONG_KH, w->resc_cap[kh], kh == 0, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, st>>>(pd);
             CUDA_TRY(ctx, cudaGetLastError());
             ++launches;
         }
@@ -731,13 +729,12 @@ extern "C" int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s,
 }
 
 // Plan-only summary (no device needed): used by the CPU test-suite to check the host logic.
-extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int packed, int seg_cols,
+extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int seg_cols,
                                  int64_t *info /* [8 + 4 * 16] */, uint8_t *pair_cover /* [n_pairs] or NULL */)
 {
     if (!fb || !info) return PHMM_ERR_ARG;
     PlanOptions o;
     o.precision = precision;
-    o.packed = packed;
     o.seg_cols = seg_cols;
     Plan P;
     std::string err;
@@ -758,8 +755,10 @@ extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int
         // walk every task the way the kernel does and count how often each pair is produced
         for (auto &cp : P.classes)
             for (auto &t : cp.tasks) {
-                int nh = 0;
-                for (int64_t col = 0; col < t.ncols; ++nh) col += P.hap_len[t.hap0 + nh] + 1;
+                const int nh = t.nh;
+                int64_t cols = 0;
+                for (int j = 0; j < nh; ++j) cols += P.hap_len[t.hap0 + j] + SEP_COLS;
+                if (cols != t.ncols || nh > MAX_RUN_HAPS) return PHMM_ERR_ARG;
                 for (int g = 0; g < cp.kc.group(); ++g) {
                     if (t.read[g] < 0) continue;
                     const ReadRec &rr = P.reads[t.read[g]];

@@ -28,11 +28,9 @@ const HostTables &host_tables();
 // ---- planner (phmm_plan.cpp) -------------------------------------------------------------------
 struct PlanOptions {
     int precision = 0;        // PHMM_OPT_PRECISION
-    int packed = 1;           // PHMM_OPT_PACKED
     int seg_cols = 0;         // 0 = adaptive
     int resident_warps = 2368;   // warps the device keeps in flight (for adaptive run sizing)
     int force_kh = 0, force_lanes = 0;   // debugging / benchmarking: pin the kernel class
-    double step_overhead = 0.9;  // per-step fixed cost in units of one register-tile row
 };
 
 struct ClassPlan {
@@ -62,19 +60,15 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
 // ---- kernels (phmm_inst_*.cu, phmm_microbench.cu) -------------------------------------------
 typedef void (*KernelF32)(const KernelParams<float>);
 typedef void (*KernelF64)(const KernelParams<double>);
-KernelF32 lookup_f32p_l32_f0(int kh);
-KernelF32 lookup_f32p_l32_f1(int kh);
-KernelF32 lookup_f32p_l16_f0(int kh);
-KernelF32 lookup_f32p_l16_f1(int kh);
-KernelF32 lookup_f32p_l8_f0(int kh);
-KernelF32 lookup_f32p_l8_f1(int kh);
-KernelF32 lookup_f32s_f0(int kh);
-KernelF32 lookup_f32s_f1(int kh);
+KernelF32 lookup_f32_l32_f0(int kh);
+KernelF32 lookup_f32_l32_f1(int kh);
+KernelF32 lookup_f32_l16_f0(int kh);
+KernelF32 lookup_f32_l16_f1(int kh);
 KernelF64 lookup_f64_f0(int kh);
 KernelF64 lookup_f64_f1(int kh);
 KernelF32 lookup_f32(const KClass &kc, bool fast);
 KernelF64 lookup_f64(int kh, bool fast);
-KernelF32 lookup_f32_long(int which);
+KernelF32 lookup_f32_long(bool fast);
 KernelF64 lookup_f64_long(bool fast);
 cudaError_t launch_pipe_bench(int which, float *out, int grid, int iters, cudaStream_t st,
                               double *ops_per_thread);

@@ -1,0 +1,18 @@
+// FP32 forward kernels (two reads per thread in f32x2 halves): 32 lanes per read pair, FMA-contracted.
+#include "phmm_kernels.cuh"
+namespace phmm {
+KernelF32 lookup_f32_l32_f1(int kh)
+{
+    switch (kh) {
+    case 1: return f32_kernel<1, 32, true>();
+    case 2: return f32_kernel<2, 32, true>();
+    case 3: return f32_kernel<3, 32, true>();
+    case 4: return f32_kernel<4, 32, true>();
+    case 5: return f32_kernel<5, 32, true>();
+    case 6: return f32_kernel<6, 32, true>();
+    case 7: return f32_kernel<7, 32, true>();
+    case 8: return f32_kernel<8, 32, true>();
+    default: return nullptr;
+    }
+}
+}  // namespace phmm

@@ -1,4 +1,4 @@
-// FP64 forward kernels (rescue path).
+// FP64 forward kernels (rescue path), FMA-contracted.
 #include "phmm_kernels.cuh"
 namespace phmm {
 KernelF64 lookup_f64_f1(int kh)

@@ -6,22 +6,29 @@
 // (tools/GKL/src/main/native/pairhmm/IntelPairHmmCSource.cpp:61-85).
 //
 // How (not a port of the AVX striping):
-//   * One warp streams ONE read (or 2/4 short reads, one per lane group) against a whole run of
-//     haplotypes of its batch, laid end to end in HBM as one-hot codes with a separator column
-//     after each haplotype.  The anti-diagonal wavefront therefore fills once per run instead
-//     of once per pair, and the read's seven per-row constants stay in registers for the run.
-//   * A thread owns VL virtual lanes of KH consecutive read rows each.  For FP32, VL = 2 and the
-//     two virtual lanes live in the two halves of Blackwell's packed f32x2 registers: the 8
-//     multiplies of a cell update issue as FMUL2 (bit-exact kernel) or everything as FFMA2
-//     (fast kernel), halving the issue slots the FMA pipe needs.  The second virtual lane runs
-//     one column behind the first, so its "up" neighbour is the first lane's previous result
-//     and only one shuffle per state array crosses threads per step.
-//   * Virtual lane v works on column (step - v).  The bottom row of each virtual lane moves to
-//     the next one through __shfl_up_sync (between threads) or a register (within a thread).
+//   * One lane group (32 or 16 threads) streams its reads against a whole run of haplotypes of
+//     their batch, laid end to end in HBM as code bytes with SEP_COLS separator columns after each
+//     haplotype.  The anti-diagonal wavefront therefore fills once per run instead of once per
+//     pair, and the reads' per-row constants stay in registers for the run.
+//   * A thread owns KH consecutive read rows.  FP32: of TWO reads at once, one in each half of
+//     Blackwell's packed f32x2 registers, so every multiply of a cell update issues as FMUL2 (and
+//     everything as FFMA2 in the fast kernel) and no value ever crosses between the halves.
+//     FP64: of one read.
+//   * Lane l works on column (step - l).  The bottom row of a thread moves to the next lane
+//     through __shfl_up_sync.
+//   * The emission factor of a cell, (match ? 1 - eps : eps / 3), is not selected per cell: it is
+//     read from a per-warp shared-memory table e[row][code][lane] (one 64-bit LDS per row and
+//     step, conflict-free), indexed by the haplotype code of the lane's current column.  Code 0
+//     (separator) maps to 0 for every row, so M and X clear themselves in separator columns.
 //   * Read rows are right-aligned: unused rows at the top are "dummy rows" whose constants make
 //     them reproduce the DP's row-0 boundary (M = X = 0, Y = INITIAL_CONSTANT / haplen) exactly,
 //     so the first real row needs no special case and the result is always the last row of the
-//     last virtual lane.
+//     last lane.
+//   * The loop body handles SEP_COLS = 4 columns: one 32-bit word of haplotype codes per thread
+//     and iteration.  A lane passes a separator run in four consecutive steps, exactly one of
+//     which is the last step of an iteration: there it resets Y to the next haplotype's column-0
+//     boundary (and the last lane emits the finished pair).  The values it carries through the
+//     rest of the separator run stay at the boundary because M = X = 0 there.
 //   * Haplotype columns are staged per warp into a shared-memory ring with 128-bit cp.async
 //     copies one 512-column chunk ahead of use.
 //   * Bit-exact kernel: __fmul_rn/__fadd_rn semantics, the reference's association order
@@ -43,13 +50,14 @@ namespace phmm {
 // ------------------------------------------------------------------------------------------
 // Arithmetic back-ends: V = register type holding VL values of T.
 // ------------------------------------------------------------------------------------------
-template <typename T, int VL, bool FAST>
+template <typename T, bool FAST>
 struct Ops;
 
-// FP32, two virtual lanes packed in f32x2.
+// FP32, two reads packed in f32x2.
 template <bool FAST>
-struct Ops<float, 2, FAST> {
+struct Ops<float, FAST> {
     typedef float2 V;
+    static constexpr int VL = 2;
     static __device__ __forceinline__ V splat(float x) { return make_float2(x, x); }
     static __device__ __forceinline__ float get(const V &a, int c) { return c ? a.y : a.x; }
     static __device__ __forceinline__ void set(V &a, int c, float x) { if (c) a.y = x; else a.x = x; }
@@ -61,29 +69,36 @@ struct Ops<float, 2, FAST> {
         return make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y));
     }
     static __device__ __forceinline__ V fma(V a, V b, V c) { return __ffma2_rn(a, b, c); }
+    static __device__ __forceinline__ V shfl_up(V v, int width)
+    {
+        return make_float2(__shfl_up_sync(FULL_MASK, v.x, 1, width), __shfl_up_sync(FULL_MASK, v.y, 1, width));
+    }
+    static __device__ __forceinline__ V lds(uint32_t addr)
+    {
+        V v;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+        return v;
+    }
 };
 
-// Scalar back-ends (FP64 rescue, FP32 guard-band re-decision, non-packed FP32 variant).
+// FP64 (rescue path), one read.
 template <bool FAST>
-struct Ops<float, 1, FAST> {
-    typedef float V;
-    static __device__ __forceinline__ V splat(float x) { return x; }
-    static __device__ __forceinline__ float get(const V &a, int) { return a; }
-    static __device__ __forceinline__ void set(V &a, int, float x) { a = x; }
-    static __device__ __forceinline__ V mul(V a, V b) { return __fmul_rn(a, b); }
-    static __device__ __forceinline__ V add(V a, V b) { return __fadd_rn(a, b); }
-    static __device__ __forceinline__ V fma(V a, V b, V c) { return __fmaf_rn(a, b, c); }
-};
-
-template <bool FAST>
-struct Ops<double, 1, FAST> {
+struct Ops<double, FAST> {
     typedef double V;
+    static constexpr int VL = 1;
     static __device__ __forceinline__ V splat(double x) { return x; }
     static __device__ __forceinline__ double get(const V &a, int) { return a; }
     static __device__ __forceinline__ void set(V &a, int, double x) { a = x; }
     static __device__ __forceinline__ V mul(V a, V b) { return __dmul_rn(a, b); }
     static __device__ __forceinline__ V add(V a, V b) { return __dadd_rn(a, b); }
     static __device__ __forceinline__ V fma(V a, V b, V c) { return __fma_rn(a, b, c); }
+    static __device__ __forceinline__ V shfl_up(V v, int width) { return __shfl_up_sync(FULL_MASK, v, 1, width); }
+    static __device__ __forceinline__ V lds(uint32_t addr)
+    {
+        V v;
+        asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+        return v;
+    }
 };
 
 template <typename T> struct Scalar;
@@ -91,13 +106,11 @@ template <> struct Scalar<float> {
     static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
     static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
     static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
-    static __device__ __forceinline__ float shfl_up(float v, int width) { return __shfl_up_sync(FULL_MASK, v, 1, width); }
 };
 template <> struct Scalar<double> {
     static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
     static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
     static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
-    static __device__ __forceinline__ double shfl_up(double v, int width) { return __shfl_up_sync(FULL_MASK, v, 1, width); }
 };
 
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
@@ -110,9 +123,8 @@ __device__ __forceinline__ void cp_async_wait_all()
     asm volatile("cp.async.wait_all;\n" ::: "memory");
 }
 
-// FP64 kernel class index of a read (list the FP32 kernel appends rescue work to):
-// scalar kernel, 32 lanes, kh rows per lane, capacity 32*kh - 1.  0 = longer than any
-// single-pass class.
+// FP64 / guard kernel class index of a read (list the FP32 kernel appends rescue work to):
+// 32 lanes, kh rows per lane, capacity 32*kh - 1.  0 = longer than any single-pass class.
 __host__ __device__ __forceinline__ int rescue_class(int rslen)
 {
     int kh = (rslen + 1 + 31) / 32;
@@ -132,15 +144,15 @@ __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float 
         const bool guard = FAST && (res >= P.guard_lo) && (res < P.guard_hi);
         if (guard || res < MIN_ACCEPTED_F) {
             // :73-75 -- below MIN_ACCEPTED the pair is re-run in FP64 (by the FP64 kernel of the
-            // read's scalar class); the fast kernel hands near-threshold sums to the bit-exact
-            // FP32 kernel first so that the rescue decision is the reference's.
+            // read's class); the fast kernel hands near-threshold sums to the bit-exact FP32
+            // kernel first so that the rescue decision is the reference's.
             Task nt;
             nt.stream_off = hap_stream_off;
-            nt.ncols = hap_len + 1;
+            nt.ncols = hap_len + SEP_COLS;
             nt.hap0 = hap_idx;
             nt.out0 = out_rel;
             nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
-            nt.pad = 0;
+            nt.nh = 1;
             const int ci = rescue_class(rslen);
             if (guard) {
                 int k = atomicAdd(&P.guard_count[ci], 1);
@@ -170,24 +182,34 @@ __device__ __forceinline__ void emit_result(const KernelParams<double> &P, doubl
 // ------------------------------------------------------------------------------------------
 // The forward kernel.  Persistent warps pull tasks from a device-side queue.
 // ------------------------------------------------------------------------------------------
-template <typename T, int VL, int KH, int LANES, bool FAST, bool LONG, int MINB>
+template <typename T, int KH, int LANES, bool FAST, bool LONG, int MINB>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
 phmm_forward_kernel(const KernelParams<T> P)
 {
-    typedef Ops<T, VL, FAST> O;
+    typedef Ops<T, FAST> O;
     typedef typename O::V V;
     typedef Scalar<T> S;
-    constexpr int NV = VL * LANES;            // virtual lanes per read
-    constexpr uint32_t RMASK = STREAM_RING - 1;
+    constexpr int VL = O::VL;
+    constexpr int ROWS = KH * LANES;          // read rows per pass
+    constexpr int ETAB = KH * N_CODES * 256;  // bytes
+    constexpr int WSM = ETAB + STREAM_RING + (MAX_RUN_HAPS + 2) * 12;
+    constexpr uint32_t WMASK = STREAM_RING / 4 - 1;
+    static_assert(sizeof(V) == 8, "emission table entries are 8 bytes");
 
-    __shared__ __align__(16) uint8_t ring_all[WARPS_PER_BLOCK][STREAM_RING];
+    extern __shared__ __align__(16) uint8_t smem_all[];
     const int lane = threadIdx.x & 31;
-    uint8_t *ring = ring_all[threadIdx.x >> 5];
-    const int gl = lane & (LANES - 1);        // lane within its read's group
+    uint8_t *etab = smem_all + (threadIdx.x >> 5) * WSM;
+    uint8_t *ring = etab + ETAB;
+    const uint32_t *ring32 = reinterpret_cast<const uint32_t *>(ring);
+    uint8_t *iytab = ring + STREAM_RING;                                   // 8-byte slots holding a T
+    int32_t *hltab = reinterpret_cast<int32_t *>(iytab + (MAX_RUN_HAPS + 2) * 8);
+    const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(etab) + lane * 8;
+    const int gl = lane & (LANES - 1);        // lane within its group
     const int grp = lane / LANES;
     const bool last_lane = (gl == LANES - 1);
     const int ntasks = *P.ntasks_ptr;
     const T zero = (T)0;
+    const uint32_t sh = ((4 - (gl & 3)) & 3) * 8;
 
     for (;;) {
         int t = 0;
@@ -200,81 +222,108 @@ phmm_forward_kernel(const KernelParams<T> P)
         const int ncols = tk->ncols;
         const int hap0 = tk->hap0;
         const int out0 = tk->out0;
-        const int rid = tk->read[grp];
-        const bool active = rid >= 0;
-        int R = 0;
-        int64_t roff = 0, out_base = 0;
-        if (active) {
-            const ReadRec rr = P.reads[rid];
-            R = rr.len; roff = rr.off; out_base = rr.out_base;
+        const int nh = tk->nh;
+        int rid[VL], R[VL];
+        int64_t roff[VL], out_base[VL];
+        int rmax = 0;
+#pragma unroll
+        for (int c = 0; c < VL; ++c) {
+            rid[c] = tk->read[grp * VL + c];
+            R[c] = 0; roff[c] = 0; out_base[c] = 0;
+            if (rid[c] >= 0) {
+                const ReadRec rr = P.reads[rid[c]];
+                R[c] = rr.len; roff[c] = rr.off; out_base[c] = rr.out_base;
+            }
+            rmax = max(rmax, R[c]);
+        }
+        // per-run haplotype table: column-0 boundary INITIAL_CONSTANT / haplen (:86) and length
+        __syncwarp();
+        for (int j = lane; j <= nh; j += 32) {
+            const int hl = P.hap_len[hap0 + j];
+            *reinterpret_cast<T *>(iytab + 8 * j) = S::div(P.init_const, (T)hl);
+            hltab[j] = hl;
         }
 
-        // Multi-pass (LONG) kernels cut the read into blocks of NV * KH rows; block `pass` reads
-        // the previous block's bottom row from spill_in and leaves its own in spill_out.
-        const int npass = LONG ? (R + NV * KH) / (NV * KH) : 1;
-        T *spill_in = nullptr, *spill_out = nullptr;
+        // Multi-pass (LONG) kernels cut the reads into blocks of ROWS rows; block `pass` reads the
+        // previous block's bottom row from spill_in and leaves its own in spill_out
+        // (index 0 = column-0 boundary of the first haplotype, index c + 1 = column c).
+        int npass = 1;
+        V *spill_in = nullptr, *spill_out = nullptr;
         int64_t spill_cols = 0;
         if (LONG) {
+            npass = (__reduce_max_sync(FULL_MASK, rmax) + ROWS) / ROWS;
             const int64_t wslot = (int64_t)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
-            spill_cols = P.scratch_stride / 6;
-            spill_in = P.scratch + wslot * P.scratch_stride;
+            spill_cols = P.scratch_stride / (6 * VL);
+            spill_in = reinterpret_cast<V *>(P.scratch + wslot * P.scratch_stride);
             spill_out = spill_in + 3 * spill_cols;
         }
       for (int pass = 0; pass < npass; ++pass) {
         const bool final_pass = (pass == npass - 1);
-        // ---- per-row constants (initializeVectors :83-128, stripeINITIALIZATION :151-158) ----
-        V pMM[KH], pG[KH], pMX[KH], pXX[KH], pMY[KH], em[KH], ex[KH];
-        V pYY0;                       // pYY of row 0 of each virtual lane (see dummy rows below)
-        uint32_t rbits[VL], dmask[VL];
-        const int nd = npass * NV * KH - R;   // dummy rows on top of block 0; always >= 1
+        // ---- per-row constants (initializeVectors :83-128, stripeINITIALIZATION :151-158) and
+        //      the emission table ----------------------------------------------------------------
+        V pMM[KH], pG[KH], pMX[KH], pXX[KH], pMY[KH];
+        V pYY0;                       // pYY of row 0 (see dummy rows below)
+        uint32_t dmask[VL];
 #pragma unroll
-        for (int c = 0; c < VL; ++c) {
-            rbits[c] = 0; dmask[c] = 0;
+        for (int c = 0; c < VL; ++c) dmask[c] = 0;
+        __syncwarp();                 // every lane is done with the previous table
 #pragma unroll
-            for (int p = 0; p < KH; ++p) {
-                const int r = pass * NV * KH + (gl * VL + c) * KH + p - nd;    // 0-based read position
-                T mm = zero, g = zero, mx = zero, xx = zero, my = zero, e1 = zero, e3 = zero, yy = zero;
+        for (int p = 0; p < KH; ++p) {
+            T em[VL], ex[VL];
+            int rcode[VL];
+#pragma unroll
+            for (int c = 0; c < VL; ++c) {
+                const int nd = npass * ROWS - R[c];                       // dummy rows on top; >= 1
+                const int r = pass * ROWS + gl * KH + p - nd;             // 0-based read position
+                T mm = zero, g = zero, mx = zero, xx = zero, my = zero, yy = zero;
+                em[c] = zero; ex[c] = zero; rcode[c] = -1;
                 if (r >= 0) {
-                    const int _q = P.q[roff + r] & 127, _i = P.i[roff + r] & 127;
-                    const int _d = P.d[roff + r] & 127, _c = P.c[roff + r] & 127;
+                    const int _q = P.q[roff[c] + r] & 127, _i = P.i[roff[c] + r] & 127;
+                    const int _d = P.d[roff[c] + r] & 127, _c = P.c[roff[c] + r] & 127;
                     const int mxq = max(_i, _d), mnq = min(_i, _d);
                     mm = P.mm[((mxq * (mxq + 1)) >> 1) + mnq];        // set_mm_prob, Context.h:120-132
                     const T pc = P.ph2pr[_c];
                     g = S::sub((T)1, pc);                             // :115
                     mx = P.ph2pr[_i]; my = P.ph2pr[_d]; xx = pc; yy = pc;
                     const T eps = P.ph2pr[_q];
-                    e1 = S::sub((T)1, eps);                           // :156
-                    e3 = S::div(eps, (T)3);                           // :158 true division
-                    uint8_t b = P.rs[roff + r];
-                    uint32_t code = (b == 'C') ? CODE_C : (b == 'T') ? CODE_T : (b == 'G') ? CODE_G
-                                  : (b == 'N') ? CODE_N : CODE_A;
-                    rbits[c] |= code << (4 * p);
+                    em[c] = S::sub((T)1, eps);                        // :156
+                    ex[c] = S::div(eps, (T)3);                        // :158 true division
+                    const uint8_t b = P.rs[roff[c] + r];
+                    rcode[c] = (b == 'C') ? CODE_C : (b == 'T') ? CODE_T : (b == 'G') ? CODE_G
+                             : (b == 'N') ? CODE_N : CODE_A;
                 } else {
                     // Dummy row: stays at (M, X, Y) = (0, 0, INITIAL_CONSTANT/haplen), the row-0
-                    // boundary (:86,:162): e = 0 kills M, pMX = 0 and a zero "up" X keep X = 0,
+                    // boundary (:86,:162): emission 0 kills M, pMX = 0 and a zero "up" X keep X = 0,
                     // pMY = 0 and pYY = 1 carry Y along the row exactly.  pXX doubles as pYY in
-                    // real rows; only row 0 of a virtual lane can see a non-zero "up" X (lane 0
-                    // receives its own registers from the shuffle), so it gets pXX = 0 and its
-                    // own pYY register.
+                    // real rows; only row 0 of a thread can see a non-zero "up" X (lane 0 receives
+                    // its own registers from the shuffle), so it gets pXX = 0 and its own pYY.
                     xx = (p == 0) ? zero : (T)1;
                     yy = (T)1;
                     dmask[c] |= 1u << p;
                 }
                 O::set(pMM[p], c, mm); O::set(pG[p], c, g); O::set(pMX[p], c, mx);
-                O::set(pXX[p], c, xx); O::set(pMY[p], c, my); O::set(em[p], c, e1);
-                O::set(ex[p], c, e3);
+                O::set(pXX[p], c, xx); O::set(pMY[p], c, my);
                 if (p == 0) O::set(pYY0, c, yy);
+            }
+            // e[p][code]: match <=> equal or either is N (precompute_masks_ :3-35); separator -> 0
+#pragma unroll
+            for (int code = 0; code < N_CODES; ++code) {
+                V ev;
+#pragma unroll
+                for (int c = 0; c < VL; ++c) {
+                    const bool match = (code == rcode[c]) || (code == CODE_N) || (rcode[c] == CODE_N);
+                    O::set(ev, c, (code == CODE_SEP || rcode[c] < 0) ? zero : (match ? em[c] : ex[c]));
+                }
+                *reinterpret_cast<V *>(etab + (p * N_CODES + code) * 256 + lane * 8) = ev;
             }
         }
 
         // ---- state: column-0 boundary -------------------------------------------------------
-        int jh[VL];
-        T initY[VL];
+        int jh = 0;
         V M[KH], X[KH], Y[KH];
+        __syncwarp();
         {
-            const T iy = S::div(P.init_const, (T)P.hap_len[hap0]);    // :86
-#pragma unroll
-            for (int c = 0; c < VL; ++c) { jh[c] = 0; initY[c] = iy; }
+            const T iy = *reinterpret_cast<const T *>(iytab);
 #pragma unroll
             for (int p = 0; p < KH; ++p) {
                 M[p] = O::splat(zero); X[p] = O::splat(zero);
@@ -283,171 +332,158 @@ phmm_forward_kernel(const KernelParams<T> P)
             }
         }
         V U1m = O::splat(zero), U1x = O::splat(zero), U1y = O::splat(zero);
-        // a later block whose block above is nothing but dummy rows sits directly under DP row 0:
-        // its diagonal neighbour at the first column is Y[0][0] = INITIAL_CONSTANT / haplen
-        if (LONG && pass > 0 && gl == 0 && nd >= pass * NV * KH) O::set(U1y, 0, initY[0]);
         V U2m, U2x, U2y;
-        T sumM = zero, sumX = zero;
+        V sumM = O::splat(zero), sumX = O::splat(zero);
         int hapstart = 0;
+        V sp_m = O::splat(zero), sp_x = O::splat(zero), sp_y = O::splat(zero);
 
         // ---- haplotype-stream ring -------------------------------------------------------------
         const int a = (int)(stream_off & 15);
         const uint8_t *sbase = P.stream + (stream_off - a);
-        const int need = a + ncols;                 // ring bytes that must hold real columns
-        const int s_end = a + ncols + NV - 1;       // loop runs s' = a .. s_end-1 (s' = step + a)
-        __syncwarp();
+        const int need = a + ncols + LANES + 16;    // ring bytes that must hold stream data
+        const int s_begin = a & ~3;                 // s = step + a; lane gl is at column s - a - gl
+        const int s_end = (a + ncols + LANES - 1 + 3) & ~3;
         if (lane < 4) *reinterpret_cast<uint4 *>(ring + STREAM_RING - 64 + 16 * lane) = make_uint4(0, 0, 0, 0);
         cp_async16(ring + 16 * lane, sbase + 16 * lane);
         if (STREAM_CHUNK < need) cp_async16(ring + STREAM_CHUNK + 16 * lane, sbase + STREAM_CHUNK + 16 * lane);
 
-        const int vpos = gl * VL;                   // first virtual lane of this thread
-        uint32_t hb_next = 0, hrep_prev = 0;
-        T sp_m = zero, sp_x = zero, sp_y = zero;
-        if (LONG && pass > 0 && gl == 0) {
-            sp_m = __ldcg(spill_in); sp_x = __ldcg(spill_in + spill_cols); sp_y = __ldcg(spill_in + 2 * spill_cols);
+        if (LONG) {
+            if (!final_pass && last_lane) {          // boundary entry for the block below
+                spill_out[0] = M[KH - 1]; spill_out[spill_cols] = X[KH - 1]; spill_out[2 * spill_cols] = Y[KH - 1];
+            }
+            if (pass > 0 && gl == 0) {
+                U1m = __ldcg(spill_in); U1x = __ldcg(spill_in + spill_cols); U1y = __ldcg(spill_in + 2 * spill_cols);
+                const int idx = min(max(s_begin - a + 1, 0), ncols);
+                sp_m = __ldcg(spill_in + idx); sp_x = __ldcg(spill_in + spill_cols + idx);
+                sp_y = __ldcg(spill_in + 2 * spill_cols + idx);
+            }
         }
 
+        uint32_t wi = (uint32_t)((s_begin >> 2) - ((gl + 3) >> 2));
+        uint32_t wprev = 0;
         for (int cb = 0, ch = 0; cb < s_end; cb += STREAM_CHUNK, ++ch) {
             cp_async_wait_all();
             __syncwarp();
             if (ch == 0) {
                 if (lane < a) ring[lane] = 0;       // columns -1 .. -a of an unaligned run
                 __syncwarp();
-                hb_next = ring[(a - vpos) & RMASK];
+                wprev = ring32[wi & WMASK];
             }
             if ((ch + 2) * STREAM_CHUNK < need)
-                cp_async16(ring + (((ch + 2) * STREAM_CHUNK) & RMASK) + 16 * lane,
+                cp_async16(ring + (((ch + 2) * STREAM_CHUNK) & (STREAM_RING - 1)) + 16 * lane,
                            sbase + (ch + 2) * STREAM_CHUNK + 16 * lane);
             const int s_hi = min(cb + STREAM_CHUNK, s_end);
-#pragma unroll 2
-            for (int s = max(cb, a); s < s_hi; ++s) {
-                // -- neighbours: bottom row of the upstream virtual lane, one and two steps ago
-                U2m = U1m; U2x = U1x; U2y = U1y;
-                {
-                    const T rm = S::shfl_up(O::get(M[KH - 1], VL - 1), LANES);
-                    const T rx = S::shfl_up(O::get(X[KH - 1], VL - 1), LANES);
-                    const T ry = S::shfl_up(O::get(Y[KH - 1], VL - 1), LANES);
-                    if (VL == 2) {
-                        O::set(U1m, 1, O::get(M[KH - 1], 0)); O::set(U1x, 1, O::get(X[KH - 1], 0));
-                        O::set(U1y, 1, O::get(Y[KH - 1], 0));
+            for (int s0 = max(cb, s_begin); s0 < s_hi; s0 += 4) {
+                ++wi;
+                const uint32_t wnext = ring32[wi & WMASK];
+                const uint32_t codes = __funnelshift_r(wprev, wnext, sh);   // codes of columns s0..s0+3 - a - gl
+                wprev = wnext;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    // -- emission factors of this column: table row (code << 8) + p * N_CODES * 256
+                    const uint32_t eaddr = ebase + __byte_perm(codes, 0, 0x4404 | (k << 4));
+                    V e[KH];
+#pragma unroll
+                    for (int p = 0; p < KH; ++p) e[p] = O::lds(eaddr + p * N_CODES * 256);
+                    // -- neighbours: bottom row of the upstream lane, one and two steps ago
+                    U2m = U1m; U2x = U1x; U2y = U1y;
+                    U1m = O::shfl_up(M[KH - 1], LANES); U1x = O::shfl_up(X[KH - 1], LANES);
+                    U1y = O::shfl_up(Y[KH - 1], LANES);
+                    if (LONG && pass > 0 && gl == 0) {      // first row of a later block: "up" is the
+                        U1m = sp_m; U1x = sp_x; U1y = sp_y; // block above
+                        const int idx = min(max(s0 + k - a + 2, 0), ncols);
+                        sp_m = __ldcg(spill_in + idx); sp_x = __ldcg(spill_in + spill_cols + idx);
+                        sp_y = __ldcg(spill_in + 2 * spill_cols + idx);
                     }
-                    if (LONG && pass > 0 && gl == 0) {     // first row of a later block: "up" is the
-                        O::set(U1m, 0, sp_m); O::set(U1x, 0, sp_x); O::set(U1y, 0, sp_y);   // block above
-                        const int ncol = s + 1 - a;
-                        if (ncol < ncols) {
-                            sp_m = __ldcg(spill_in + ncol); sp_x = __ldcg(spill_in + spill_cols + ncol);
-                            sp_y = __ldcg(spill_in + 2 * spill_cols + ncol);
+                    // -- cell updates (computeMXY :183-198)
+                    V nM[KH], nX[KH], nY[KH];
+#pragma unroll
+                    for (int p = 0; p < KH; ++p) {
+                        const V dm = p ? M[p - 1] : U2m;
+                        const V dx = p ? X[p - 1] : U2x;
+                        const V dy = p ? Y[p - 1] : U2y;
+                        const V yy = p ? pXX[p] : pYY0;
+                        if (FAST) {
+                            nM[p] = O::mul(O::fma(dm, pMM[p], O::mul(O::add(dx, dy), pG[p])), e[p]);
+                            nY[p] = O::fma(M[p], pMY[p], O::mul(Y[p], yy));
+                        } else {
+                            nM[p] = O::mul(O::add(O::add(O::mul(dm, pMM[p]), O::mul(dx, pG[p])),
+                                                  O::mul(dy, pG[p])), e[p]);
+                            nY[p] = O::add(O::mul(M[p], pMY[p]), O::mul(Y[p], yy));
                         }
-                    } else {
-                        O::set(U1m, 0, rm); O::set(U1x, 0, rx); O::set(U1y, 0, ry);
+                    }
+#pragma unroll
+                    for (int p = 0; p < KH; ++p) {
+                        const V um = p ? nM[p - 1] : U1m;
+                        const V ux = p ? nX[p - 1] : U1x;
+                        if (FAST) nX[p] = O::fma(ux, pXX[p], O::mul(um, pMX[p]));
+                        else      nX[p] = O::add(O::mul(um, pMX[p]), O::mul(ux, pXX[p]));
+                    }
+#pragma unroll
+                    for (int p = 0; p < KH; ++p) { M[p] = nM[p]; X[p] = nX[p]; Y[p] = nY[p]; }
+                    // -- last-row sums (:328,:331): two separate sequential sums in column order
+                    //    (separator columns add exact zeros)
+                    sumM = O::add(sumM, M[KH - 1]);
+                    sumX = O::add(sumX, X[KH - 1]);
+                    if (LONG && !final_pass && last_lane) {
+                        const int col = s0 + k - a - gl;
+                        if (col >= 0 && col < ncols) {
+                            spill_out[col + 1] = M[KH - 1];
+                            spill_out[spill_cols + col + 1] = X[KH - 1];
+                            spill_out[2 * spill_cols + col + 1] = Y[KH - 1];
+                        }
                     }
                 }
-                // -- haplotype code of this step's column (prefetched) and of the next one
-                const uint32_t hb = hb_next;
-                hb_next = ring[(s + 1 - vpos) & RMASK];
-                uint32_t hbits[VL];
-                hbits[0] = __byte_perm(hb, 0, 0);           // code in all 8 nibbles
-                if (VL == 2) hbits[1] = hrep_prev;          // second virtual lane: one column behind
-                hrep_prev = hbits[0];
-
-                // -- cell updates (computeMXY :183-198)
-                V nM[KH], nX[KH], nY[KH];
-#pragma unroll
-                for (int p = 0; p < KH; ++p) {
-                    const V dm = p ? M[p - 1] : U2m;
-                    const V dx = p ? X[p - 1] : U2x;
-                    const V dy = p ? Y[p - 1] : U2y;
-                    V e;
-#pragma unroll
-                    for (int c = 0; c < VL; ++c) {
-                        const bool match = (rbits[c] & hbits[c] & (0xFu << (4 * p))) != 0;
-                        O::set(e, c, match ? O::get(em[p], c) : O::get(ex[p], c));
-                    }
-                    const V yy = p ? pXX[p] : pYY0;
-                    if (FAST) {
-                        nM[p] = O::mul(O::fma(dy, pG[p], O::fma(dx, pG[p], O::mul(dm, pMM[p]))), e);
-                        nY[p] = O::fma(M[p], pMY[p], O::mul(Y[p], yy));
-                    } else {
-                        nM[p] = O::mul(O::add(O::add(O::mul(dm, pMM[p]), O::mul(dx, pG[p])),
-                                              O::mul(dy, pG[p])), e);
-                        nY[p] = O::add(O::mul(M[p], pMY[p]), O::mul(Y[p], yy));
-                    }
-                }
-#pragma unroll
-                for (int p = 0; p < KH; ++p) {
-                    const V um = p ? nM[p - 1] : U1m;
-                    const V ux = p ? nX[p - 1] : U1x;
-                    if (FAST) nX[p] = O::fma(um, pMX[p], O::mul(ux, pXX[p]));
-                    else      nX[p] = O::add(O::mul(um, pMX[p]), O::mul(ux, pXX[p]));
-                }
-#pragma unroll
-                for (int p = 0; p < KH; ++p) { M[p] = nM[p]; X[p] = nX[p]; Y[p] = nY[p]; }
-
-                // -- separator / padding columns (code 0): emit, then reset to the column-0 boundary
-                bool z = (hbits[0] == 0);
-                if (VL == 2) z = z || (hbits[1] == 0);
+                // -- separator run: the step that ends an iteration resets the lane to the next
+                //    haplotype's column-0 boundary; the last lane emits the finished pair first
+                const bool z = ((codes >> 24) == 0) && (s0 + 3 - a - gl >= 0) && (jh < nh);
                 if (__any_sync(FULL_MASK, z)) {
+                    if (z) {
+                        if (last_lane && final_pass) {
+                            const int hl = hltab[jh];
 #pragma unroll
-                    for (int c = 0; c < VL; ++c) {
-                        if (hbits[c] == 0) {
-                            const int col = s - a - (vpos + c);
-                            if (col >= 0 && col < ncols) {          // separator after haplotype jh[c]
-                                if (c == VL - 1) {
-                                    if (last_lane && active && final_pass) {
-                                        const T res = S::add(sumM, sumX);   // :342
-                                        emit_result<FAST>(P, res, out_base + out0 + jh[c],
-                                                          stream_off + hapstart, col - hapstart,
-                                                          hap0 + jh[c], out0 + jh[c], rid, R);
-                                    }
-                                    sumM = zero; sumX = zero; hapstart = col + 1;
+                            for (int c = 0; c < VL; ++c)
+                                if (rid[c] >= 0) {
+                                    const T res = S::add(O::get(sumM, c), O::get(sumX, c));   // :342
+                                    emit_result<FAST>(P, res, out_base[c] + out0 + jh, stream_off + hapstart, hl,
+                                                      hap0 + jh, out0 + jh, rid[c], R[c]);
                                 }
-                                jh[c]++;
-                                initY[c] = S::div(P.init_const, (T)P.hap_len[hap0 + jh[c]]);
-                            }
-#pragma unroll
-                            for (int p = 0; p < KH; ++p) {
-                                O::set(M[p], c, zero); O::set(X[p], c, zero);
-                                O::set(Y[p], c, ((dmask[c] >> p) & 1) ? initY[c] : zero);
-                            }
+                            hapstart += hl + SEP_COLS;
                         }
-                    }
-                }
-                // -- last-row sums (:328,:331): two separate sequential sums in column order
-                sumM = S::add(sumM, O::get(M[KH - 1], VL - 1));
-                sumX = S::add(sumX, O::get(X[KH - 1], VL - 1));
-                if (LONG && !final_pass && last_lane) {
-                    const int col = s - a - (NV - 1);
-                    if (col >= 0 && col < ncols) {
-                        spill_out[col] = O::get(M[KH - 1], VL - 1);
-                        spill_out[spill_cols + col] = O::get(X[KH - 1], VL - 1);
-                        spill_out[2 * spill_cols + col] = O::get(Y[KH - 1], VL - 1);
+                        sumM = O::splat(zero); sumX = O::splat(zero);
+                        ++jh;
+                        const T iy = *reinterpret_cast<const T *>(iytab + 8 * jh);
+#pragma unroll
+                        for (int p = 0; p < KH; ++p)
+#pragma unroll
+                            for (int c = 0; c < VL; ++c) O::set(Y[p], c, ((dmask[c] >> p) & 1) ? iy : zero);
                     }
                 }
             }
         }
+        cp_async_wait_all();
         if (LONG) {
             __syncwarp();
-            T *tmp = spill_in; spill_in = spill_out; spill_out = tmp;
+            V *tmp = spill_in; spill_in = spill_out; spill_out = tmp;
         }
       }   // pass
     }
 }
 
-// Minimum resident blocks per SM requested from ptxas (caps registers per thread):
-// rows per thread K = VL * KH need about 10 K (+25) 32-bit registers in FP32, twice that in FP64.
-template <typename T, int VL, int KH>
+// Minimum resident blocks per SM requested from ptxas (caps registers per thread).
+template <typename T, int KH>
 struct MinBlocks {
-    static constexpr int K = VL * KH * (sizeof(T) / 4);
-    static constexpr int value = K <= 2 ? 8 : K <= 4 ? 6 : K <= 6 ? 5 : K <= 8 ? 4 : K <= 12 ? 3 : 2;
+    static constexpr int K = KH * (sizeof(T) / 4);
+    static constexpr int value = K <= 2 ? 6 : K <= 4 ? 4 : K <= 6 ? 3 : 2;
 };
 
 typedef void (*KernelF32)(const KernelParams<float>);
 typedef void (*KernelF64)(const KernelParams<double>);
 
-template <int VL, int KH, int LANES, bool FAST, bool LONG = false>
-static KernelF32 f32_kernel() { return phmm_forward_kernel<float, VL, KH, LANES, FAST, LONG, MinBlocks<float, VL, KH>::value>; }
+template <int KH, int LANES, bool FAST, bool LONG = false>
+static KernelF32 f32_kernel() { return phmm_forward_kernel<float, KH, LANES, FAST, LONG, MinBlocks<float, KH>::value>; }
 template <int KH, bool FAST, bool LONG = false>
-static KernelF64 f64_kernel() { return phmm_forward_kernel<double, 1, KH, 32, FAST, LONG, MinBlocks<double, 1, KH>::value>; }
+static KernelF64 f64_kernel() { return phmm_forward_kernel<double, KH, 32, FAST, LONG, MinBlocks<double, KH>::value>; }
 
 }  // namespace phmm
 #endif

@@ -17,35 +17,19 @@ namespace phmm {
 
 bool choose_class(int rslen, const PlanOptions &opt, KClass *out)
 {
+    const int vl = opt.precision == 2 ? 1 : 2;
     if (opt.force_kh > 0 && opt.force_lanes > 0) {
-        KClass kc{opt.force_kh, opt.force_lanes, (opt.packed && opt.precision != 2) ? 2 : 1, 0};
+        KClass kc{opt.force_kh, opt.precision == 2 ? 32 : opt.force_lanes, vl, 0};
         if (kc.capacity() >= rslen) { *out = kc; return true; }
     }
-    bool found = false;
-    double best = 0;
-    auto consider = [&](int kh, int lanes, int vl) {
-        KClass kc{kh, lanes, vl, 0};
-        if (kc.capacity() < rslen) return;
-        // issue slots per column ~ lanes x (tile rows + fixed per-step work); the wavefront
-        // fill/drain (vl * lanes - 1 steps per run) is a second-order term added per task
-        const double cost = lanes * (kh + opt.step_overhead / vl) * vl;
-        if (!found || cost < best - 1e-9) { found = true; best = cost; *out = kc; }
-    };
-    if (opt.packed && opt.precision != 2) {
-        for (int kh = 1; kh <= 6; ++kh) consider(kh, 8, 2);
-        for (int kh = 1; kh <= 6; ++kh) consider(kh, 16, 2);
-        for (int kh = 1; kh <= 4; ++kh) consider(kh, 32, 2);
-    } else {
-        for (int kh = 1; kh <= MAX_KH_SCALAR; ++kh) consider(kh, 32, 1);
-    }
-    if (!found) {
-        // longer than every single-pass class: multi-pass kernel
-        if (opt.precision == 2) *out = KClass{LONG_KH_F64, 32, 1, 1};
-        else if (opt.packed) *out = KClass{LONG_KH_F32, 32, 2, 1};
-        else *out = KClass{LONG_KH_F32S, 32, 1, 1};
-        found = true;
-    }
-    return found;
+    // Fewest padded rows wins; the register-file-bound cell update costs the same per row in
+    // every class.  16 lanes (two read pairs per warp, half the wavefront fill) for rows that fit,
+    // 32 lanes above; FP64 always 32 lanes.
+    const int rows = rslen + 1;                // + the dummy row that carries DP row 0
+    if (vl == 2 && rows <= 16 * MAX_KH) { *out = KClass{(rows + 15) / 16, 16, vl, 0}; return true; }
+    if (rows <= 32 * MAX_KH) { *out = KClass{(rows + 31) / 32, 32, vl, 0}; return true; }
+    *out = KClass{LONG_KH, 32, vl, 1};         // longer than every single-pass class: multi-pass
+    return true;
 }
 
 static int scalar_class_of(int rslen)
@@ -98,7 +82,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
         P.max_haplen = std::max(P.max_haplen, len);
     }
 
-    // ---- haplotype stream: code | code << 4 per column, one 0 separator after each haplotype,
+    // ---- haplotype stream: one code byte per column, SEP_COLS zero columns after each haplotype,
     //      every batch's first column 16-byte aligned (cp.async granularity) ---------------------
     std::vector<int64_t> hap_col(fb.n_haps + 1, 0);
     {
@@ -107,7 +91,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
             total = (total + 15) & ~(int64_t)15;
             for (int k = 0; k < fb.batch_num_haps[b]; ++k, ++h) {
                 hap_col[h] = total;
-                total += fb.hap_len[h] + 1;
+                total += fb.hap_len[h] + SEP_COLS;
             }
         }
         hap_col[fb.n_haps] = total;
@@ -117,10 +101,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
             const uint8_t *src = fb.hap + fb.hap_off[h];
             uint8_t *dst = P.stream.data() + hap_col[h];
             const int len = fb.hap_len[h];
-            for (int k = 0; k < len; ++k) {
-                const uint8_t cde = base_code(src[k]);
-                dst[k] = (uint8_t)(cde | (cde << 4));
-            }
+            for (int k = 0; k < len; ++k) dst[k] = base_code(src[k]);
             P.hap_len[h] = len;
         }
     }
@@ -162,9 +143,9 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
         for (int64_t b = 0; b < fb.n_batches; ++b) {
             const int bnr = fb.batch_num_reads[b], bnh = fb.batch_num_haps[b];
             int64_t runs = 0, acc = 0;
-            for (int k = 0; k < bnh; ++k) {
-                acc += fb.hap_len[h0 + k] + 1;
-                if (acc >= cols || k == bnh - 1) { ++runs; acc = 0; }
+            for (int k = 0, n_in = 0; k < bnh; ++k) {
+                acc += fb.hap_len[h0 + k] + SEP_COLS;
+                if (acc >= cols || ++n_in >= MAX_RUN_HAPS || k == bnh - 1) { ++runs; acc = 0; n_in = 0; }
             }
             std::fill(per_class.begin(), per_class.end(), 0);
             for (int k = 0; k < bnr; ++k) per_class[read_class[r0 + k]]++;
@@ -195,18 +176,38 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
             rr.batch = (int32_t)b;
             rr.out_base = out0 + (int64_t)k * bnh;
             by_class[read_class[r]].push_back((int32_t)r);
-            ClassPlan &cp = P.classes[read_class[r]];
-            cp.cells += (int64_t)rr.len * sum_h;
-            cp.pairs += bnh;
             P.n_cells += (int64_t)rr.len * sum_h;
             P.resc_cap[scalar_class_of(rr.len)] += bnh;
         }
+        // a class's leftover reads (fewer than one full task) move up to the next larger class of
+        // the batch, where they fill slots instead of leaving half a warp idle
+        {
+            std::vector<int> order;
+            for (size_t c = 0; c < P.classes.size(); ++c)
+                if (!by_class[c].empty()) order.push_back((int)c);
+            std::sort(order.begin(), order.end(), [&](int x, int y) {
+                const KClass &kx = P.classes[x].kc, &ky = P.classes[y].kc;
+                if (kx.longr != ky.longr) return kx.longr < ky.longr;
+                return kx.capacity() < ky.capacity();
+            });
+            for (size_t oi = 0; oi + 1 < order.size(); ++oi) {
+                std::vector<int32_t> &src = by_class[order[oi]], &dst = by_class[order[oi + 1]];
+                const size_t rem = src.size() % (size_t)P.classes[order[oi]].kc.group();
+                for (size_t j = 0; j < rem; ++j) { dst.push_back(src.back()); src.pop_back(); }
+            }
+        }
+        if (bnh > 0)
+            for (size_t c = 0; c < P.classes.size(); ++c)
+                for (int32_t r : by_class[c]) {
+                    P.classes[c].cells += (int64_t)P.reads[r].len * sum_h;
+                    P.classes[c].pairs += bnh;
+                }
         // runs of consecutive haplotypes
         int k = 0;
         while (k < bnh) {
             int k1 = k;
             int64_t acc = 0;
-            while (k1 < bnh && acc < seg_cols) { acc += fb.hap_len[h0 + k1] + 1; ++k1; }
+            while (k1 < bnh && acc < seg_cols && k1 - k < MAX_RUN_HAPS) { acc += fb.hap_len[h0 + k1] + SEP_COLS; ++k1; }
             for (size_t c = 0; c < P.classes.size(); ++c) {
                 const std::vector<int32_t> &rl = by_class[c];
                 const int g = P.classes[c].kc.group();
@@ -218,7 +219,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
                     t.out0 = k;
                     for (int j = 0; j < MAX_GROUP; ++j)
                         t.read[j] = (j < g && i + j < rl.size()) ? rl[i + j] : -1;
-                    t.pad = 0;
+                    t.nh = k1 - k;
                     P.classes[c].tasks.push_back(t);
                     if (P.classes[c].kc.longr) P.long_max_cols = std::max(P.long_max_cols, t.ncols);
                 }

@@ -6,11 +6,13 @@
 
 namespace phmm {
 
-// Match code per base, one-hot so that "read base matches haplotype base" is (rb & hb) != 0 and
-// N on either side matches everything -- the rule precompute_masks_ builds
-// (avx-pairhmm-template.h:3-35) on top of ConvertChar (pairhmm_common.h:30-43; every byte that
-// is not ACGTN converts to 0 = 'A').  0 never matches: it marks separator / padding columns.
-static const uint8_t CODE_A = 1, CODE_C = 2, CODE_T = 4, CODE_G = 8, CODE_N = 15;
+// Haplotype-stream code per base: the row index of the per-warp emission table.  The match rule is
+// the one precompute_masks_ builds (avx-pairhmm-template.h:3-35) on top of ConvertChar
+// (pairhmm_common.h:30-43; every byte that is not ACGTN converts to 0 = 'A'): read base matches
+// haplotype base when they are equal or either is N.  0 marks separator / padding columns, whose
+// emission is 0 for every row.
+static const uint8_t CODE_SEP = 0, CODE_A = 1, CODE_C = 2, CODE_T = 3, CODE_G = 4, CODE_N = 5;
+static const int N_CODES = 6;
 
 static inline uint8_t base_code(uint8_t b)
 {
@@ -31,42 +33,51 @@ struct ReadRec {
     int32_t batch;
 };
 
-// One unit of work for one warp: up to MAX_GROUP reads (one per lane group) streamed against
-// the same run of haplotype-stream columns.  The FP32 kernel also emits these (one read, one
-// haplotype) as FP64-rescue / guard-band work.
+// One unit of work for one warp: up to MAX_GROUP reads streamed against the same run of
+// consecutive haplotypes of their batch.  FP32 kernels hold two reads per lane group (one per
+// f32x2 half): read[2 * group + half]; FP64 kernels one: read[group].  The FP32 kernels also emit
+// these (one read, one haplotype) as FP64-rescue / guard-band work.
 static const int MAX_GROUP = 4;
 struct Task {
     int64_t stream_off;  // first column of the run in the haplotype stream
-    int32_t ncols;       // columns incl. one separator after every haplotype
+    int32_t ncols;       // columns incl. SEP_COLS separator columns after every haplotype
     int32_t hap0;        // index of the run's first haplotype in the haplotype tables
     int32_t out0;        // added to ReadRec::out_base: index of that haplotype within its batch
-    int32_t read[MAX_GROUP];   // ReadRec indices, -1 = lane group idle
-    int32_t pad;
+    int32_t read[MAX_GROUP];   // ReadRec indices, -1 = slot idle
+    int32_t nh;          // haplotypes in the run (<= MAX_RUN_HAPS)
 };
 
-// Kernel class = how a read is laid over a warp.
-//   kh    rows per virtual lane (register tile height)
-//   lanes threads per read (32, 16 or 8); a warp works on 32/lanes reads at once
-//   vl    virtual lanes per thread: 2 = FP32 packed f32x2 (Blackwell FMUL2/FFMA2), 1 = scalar
-// capacity = vl * kh * lanes - 1 read rows (row 0 of the first virtual lane is always a dummy
-// row that re-creates the DP's row-0 boundary, so no per-step select is needed there).
+// Kernel class = how reads are laid over a warp.
+//   kh    rows per thread (register tile height)
+//   lanes threads per read (32 or 16); a warp works on 32/lanes lane groups at once
+//   vl    reads per lane group: 2 = FP32, one read in each half of Blackwell's packed f32x2
+//         registers (FMUL2/FFMA2); 1 = FP64
+// capacity = kh * lanes - 1 read rows (row 0 of the first lane is always a dummy row that
+// re-creates the DP's row-0 boundary, so no per-step select is needed there).
 //   longr 1 = multi-pass kernel for reads longer than any single-pass class: the read is cut
-//         into blocks of vl * kh * lanes rows, processed one block per pass over the same columns;
+//         into blocks of kh * lanes rows, processed one block per pass over the same columns;
 //         the bottom row of a block travels to the next pass through an HBM scratch row
 //         (the reference does the same one level down with its shiftOut arrays,
 //         avx-pairhmm-template.h:224,265-297).
 struct KClass {
     int kh, lanes, vl, longr;
-    int capacity() const { return longr ? 0x7fffffff : vl * kh * lanes - 1; }
-    int group() const { return 32 / lanes; }
+    int capacity() const { return longr ? 0x7fffffff : kh * lanes - 1; }
+    int group() const { return (32 / lanes) * vl; }      // reads per task
 };
 
+static const int SEP_COLS = 4;                // separator columns after each haplotype (= columns per loop iteration)
+static const int MAX_RUN_HAPS = 62;           // haplotypes per run: per-warp table of INITIAL_CONSTANT / haplen
 static const int STREAM_CHUNK = 512;          // haplotype-stream bytes staged per cp.async round
 static const int STREAM_RING = 2048;          // per-warp shared-memory ring (4 chunks)
 static const int STREAM_SLACK = 2 * STREAM_CHUNK + 128;   // readable bytes past the last column
 static const int WARPS_PER_BLOCK = 4;
-static const int LONG_KH_F32 = 4, LONG_KH_F32S = 8, LONG_KH_F64 = 4;   // register tiles of the multi-pass kernels
-static const int MAX_KH_SCALAR = 8;           // scalar single-pass classes: 32 lanes x kh rows, kh <= 8
+static const int MAX_KH = 8;                  // single-pass classes: kh <= 8 (255 rows at 32 lanes)
+static const int LONG_KH = 8;                 // register tile of the multi-pass kernels
+static const int MAX_KH_SCALAR = MAX_KH;      // FP64 rescue classes: 32 lanes x kh rows
+
+// dynamic shared memory per warp: emission table [kh][N_CODES][32 lanes] of 8 bytes, the stream
+// ring, and the per-run haplotype table (INITIAL_CONSTANT / haplen as 8 bytes + length)
+static inline int smem_per_warp(int kh) { return kh * N_CODES * 256 + STREAM_RING + (MAX_RUN_HAPS + 2) * 12; }
 
 template <typename T>
 struct KernelParams {

@@ -18,7 +18,7 @@ from .batches import FlatBatches
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libphmm_cuda.so")
 
-OPT_PRECISION, OPT_FP32_KERNEL, OPT_FP64_KERNEL, OPT_SEG_COLS, OPT_PACKED, OPT_FORCE_CLASS = 1, 2, 3, 4, 5, 6
+OPT_PRECISION, OPT_FP32_KERNEL, OPT_FP64_KERNEL, OPT_SEG_COLS, OPT_FORCE_CLASS = 1, 2, 3, 4, 6
 BOTH, FLOAT_ONLY, DOUBLE_ONLY = 0, 1, 2
 ERRORS = {1: "PHMM_ERR_ARG", 2: "PHMM_ERR_EMPTY_SEQ", 3: "PHMM_ERR_TOO_LONG", 4: "PHMM_ERR_CUDA",
           5: "PHMM_ERR_NOMEM", 6: "PHMM_ERR_PARSE", 7: "PHMM_ERR_IO"}
@@ -145,12 +145,12 @@ def partition_lpt(cost, parts: int) -> np.ndarray:
     return owner
 
 
-def plan_summary(fb: FlatBatches, precision=0, packed=1, seg_cols=0, cover=True):
+def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True):
     lib = load_library()
     keep = _Keep(fb)
     info = np.zeros(8 + 64, np.int64)
     cov = np.zeros(max(1, fb.n_pairs), np.uint8) if cover else None
-    rc = lib.phmm_plan_summary(C.byref(keep.c), C.c_int(precision), C.c_int(packed), C.c_int(seg_cols),
+    rc = lib.phmm_plan_summary(C.byref(keep.c), C.c_int(precision), C.c_int(seg_cols),
                                _ptr(info), _ptr(cov) if cover else None)
     if rc:
         raise PhmmError(rc, "phmm_plan_summary")
@@ -219,7 +219,7 @@ class PairHMM:
     """One context on one B200 (phmm_create = the reference's initPairHMM)."""
 
     def __init__(self, device: int = 0, precision: int = BOTH, fast: bool = False, fast64: bool = False,
-                 packed: bool = True, seg_cols: int = 0, force_class=None):
+                 seg_cols: int = 0, force_class=None):
         self.lib = load_library()
         self._h = C.c_void_p()
         rc = self.lib.phmm_create(C.c_int(device), C.byref(self._h))
@@ -228,7 +228,6 @@ class PairHMM:
         self.set_option(OPT_PRECISION, precision)
         self.set_option(OPT_FP32_KERNEL, int(fast))
         self.set_option(OPT_FP64_KERNEL, int(fast64))
-        self.set_option(OPT_PACKED, int(packed))
         self.set_option(OPT_SEG_COLS, seg_cols)
         if force_class:
             self.set_option(OPT_FORCE_CLASS, (force_class[0] << 8) | force_class[1])

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define PHMM_ABI_VERSION 1
+#define PHMM_ABI_VERSION 2
 
 /* ---- status codes (the reference defines none: it asserts / exit(0)s) ---- */
 #define PHMM_OK              0
@@ -109,8 +109,6 @@ typedef struct {
                                       so the FP64-rescue set stays identical                    */
 #define PHMM_OPT_FP64_KERNEL 3   /* 0 bit-exact (unfused), 1 FMA-contracted (|rel err| ~1e-13)  */
 #define PHMM_OPT_SEG_COLS    4   /* target haplotype-stream columns per task (load balancing)    */
-#define PHMM_OPT_PACKED      5   /* 1 (default) FP32 kernel uses Blackwell packed f32x2 math
-                                    (FMUL2/FFMA2), 0 scalar FMUL/FADD/FFMA                       */
 #define PHMM_OPT_FORCE_CLASS 6   /* benchmarking: pin the kernel class, value = kh << 8 | lanes
                                     (0 = choose per read length); also env PHMM_FORCE_CLASS=kh,lanes */
 
@@ -197,7 +195,7 @@ int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s, float *ms)
  * pair_cover[p] is incremented once for every task that produces pair p. */
 int phmm_get_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d, float *consts_f,
                     double *consts_d);
-int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int packed, int seg_cols,
+int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int seg_cols,
                       int64_t *info, uint8_t *pair_cover);
 
 #ifdef __cplusplus

@@ -6,7 +6,7 @@ from conftest import load_golden
 from genomicsbench_palisade_b200 import phmm
 fb, g = load_golden("edge")
 rsl, hpl, _, _ = fb.pairs()
-for label, kw in [("both", dict()), ("double-only", dict(precision=2)), ("float-only", dict(precision=1)), ("scalar", dict(packed=False))]:
+for label, kw in [("both", dict()), ("double-only", dict(precision=2)), ("float-only", dict(precision=1))]:
     eng = phmm.PairHMM(**kw)
     w = eng.workload(fb); st = w.run(); out, raw32, raw64, resc = w.results(raw=True); w.close(); eng.close()
     want = {"both": g["out"], "double-only": g["out_f64only"], "float-only": g["out_f32only"], "scalar": g["out"]}[label]

@@ -35,8 +35,7 @@ def main():
     c1 = synth.c1_small(0.05)
     c4 = synth.c4_stress(1200)
     ok = True
-    for label, kw in [("packed-exact", dict()), ("scalar-exact", dict(packed=False)),
-                      ("packed-fast", dict(fast=True)), ("scalar-fast", dict(packed=False, fast=True)),
+    for label, kw in [("packed-exact", dict()), ("packed-fast", dict(fast=True)),
                       ("packed-exact-f64fast", dict(fast64=True))]:
         eng = phmm.PairHMM(**kw)
         exact = "exact" in label and "f64fast" not in label
@@ -60,10 +59,8 @@ def main():
     # kernel-class sweep on a C2-shaped workload
     fb = synth.c2_large(400_000)
     print("SWEEP workload pairs %d cells %.3e" % (fb.n_pairs, fb.n_cells), flush=True)
-    for label, kw in [("auto packed exact", dict()), ("auto packed fast", dict(fast=True)),
-                      ("auto scalar exact", dict(packed=False)), ("auto scalar fast", dict(packed=False, fast=True)),
-                      ("p kh4 l32 exact", dict(force_class=(4, 32))), ("p kh4 l32 fast", dict(force_class=(4, 32), fast=True)),
-                      ("s kh8 l32 exact", dict(packed=False, force_class=(8, 32))), ("s kh8 l32 fast", dict(packed=False, force_class=(8, 32), fast=True))]:
+    for label, kw in [("auto exact", dict()), ("auto fast", dict(fast=True)),
+                      ("kh8 l32 exact", dict(force_class=(8, 32))), ("kh8 l32 fast", dict(force_class=(8, 32), fast=True))]:
         try:
             eng = phmm.PairHMM(**kw)
             w = eng.workload(fb)
