@@ -290,7 +290,7 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
         tot += P.resc_cap[k];
     }
     w->resc_total = tot;
-    const bool need_resc = (w->precision == 0);
+    const bool need_resc = (w->precision != 2);   // mode 1 still needs the fast kernel's guard list
 
     const int64_t pool_len = P.pool_hi - P.pool_lo;
     w->pool_stride = (pool_len + 255) & ~(int64_t)255;
@@ -452,8 +452,8 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
         CUDA_TRY(ctx, cudaGetLastError());
         ++launches;
     }
-    // ---- fast kernel only: near-threshold pairs re-decided by the bit-exact kernel ---------------
-    if (mode == 0 && fast32) {
+    // ---- fast kernel only: near-threshold and non-finite sums re-decided by the bit-exact kernel ----
+    if (mode != 2 && fast32) {
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (w->resc_cap[kh] == 0) continue;
             KernelF32 k = kh ? lookup_f32_l32_f0(kh) : lookup_f32_long(false);

@@ -140,29 +140,29 @@ __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float 
                                             int out_rel, int rid, int rslen)
 {
     P.raw32[oidx] = res;
-    if (P.mode == 0) {
-        const bool guard = FAST && (res >= P.guard_lo) && (res < P.guard_hi);
-        if (guard || res < MIN_ACCEPTED_F) {
-            // :73-75 -- below MIN_ACCEPTED the pair is re-run in FP64 (by the FP64 kernel of the
-            // read's class); the fast kernel hands near-threshold sums to the bit-exact FP32
-            // kernel first so that the rescue decision is the reference's.
-            Task nt;
-            nt.stream_off = hap_stream_off;
-            nt.ncols = hap_len + SEP_COLS;
-            nt.hap0 = hap_idx;
-            nt.out0 = out_rel;
-            nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
-            nt.nh = 1;
-            const int ci = rescue_class(rslen);
-            if (guard) {
-                int k = atomicAdd(&P.guard_count[ci], 1);
-                P.guard[P.resc_off[ci] + k] = nt;
-            } else {
-                int k = atomicAdd(&P.resc_count[ci], 1);
-                P.resc[P.resc_off[ci] + k] = nt;
-            }
-            return;
+    // Fast kernel: a sum inside the guard band around MIN_ACCEPTED, or a non-finite one (overflow
+    // of the scaled recurrence), is re-decided by the bit-exact FP32 kernel.
+    const bool redo = FAST && (!(res <= 3.402823466e+38f) ||
+                               (P.mode == 0 && res >= P.guard_lo && res < P.guard_hi));
+    if (redo || (P.mode == 0 && res < MIN_ACCEPTED_F)) {
+        // :73-75 -- below MIN_ACCEPTED the pair is re-run in FP64 (by the FP64 kernel of the
+        // read's class).
+        Task nt;
+        nt.stream_off = hap_stream_off;
+        nt.ncols = hap_len + SEP_COLS;
+        nt.hap0 = hap_idx;
+        nt.out0 = out_rel;
+        nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
+        nt.nh = 1;
+        const int ci = rescue_class(rslen);
+        if (redo) {
+            int k = atomicAdd(&P.guard_count[ci], 1);
+            P.guard[P.resc_off[ci] + k] = nt;
+        } else {
+            int k = atomicAdd(&P.resc_count[ci], 1);
+            P.resc[P.resc_off[ci] + k] = nt;
         }
+        return;
     }
     // :78 (and :97) -- log10 in float, subtraction in float, then widened
     P.out[oidx] = (double)__fsub_rn(log10f(res), P.log10_init);
@@ -190,6 +190,11 @@ phmm_forward_kernel(const KernelParams<T> P)
     typedef typename O::V V;
     typedef Scalar<T> S;
     constexpr int VL = O::VL;
+    // Scaled recurrence of the fast FP32 single-pass kernels (6 + NTOP / KH packed FP instructions
+    // per cell instead of 8; see "scaled recurrence" in the cell update below).
+    constexpr bool SCALED = FAST && !LONG && (sizeof(T) == 4);
+    constexpr int NTOP = (KH + 3) / 4;                 // groups of chained rows per thread
+    constexpr int GRP = (KH + NTOP - 1) / NTOP;        // rows per group (<= 4): group tops at p % GRP == 0
     constexpr int ROWS = KH * LANES;          // read rows per pass
     constexpr int ETAB = KH * N_CODES * 256;  // bytes
     constexpr int WSM = ETAB + STREAM_RING + (MAX_RUN_HAPS + 2) * 12;
@@ -297,8 +302,12 @@ phmm_forward_kernel(const KernelParams<T> P)
                     // pMY = 0 and pYY = 1 carry Y along the row exactly.  pXX doubles as pYY in
                     // real rows; only row 0 of a thread can see a non-zero "up" X (lane 0 receives
                     // its own registers from the shuffle), so it gets pXX = 0 and its own pYY.
-                    xx = (p == 0) ? zero : (T)1;
+                    // (Scaled recurrence: pXX only multiplies Y there, the "up" X of row 0 is cut
+                    // through K2 instead, and a dummy row's pGAPM of 1 is what the row above folds
+                    // into its Y.)
+                    xx = (p == 0 && !SCALED) ? zero : (T)1;
                     yy = (T)1;
+                    if (SCALED) g = (T)1;
                     dmask[c] |= 1u << p;
                 }
                 O::set(pMM[p], c, mm); O::set(pG[p], c, g); O::set(pMX[p], c, mx);
@@ -318,6 +327,53 @@ phmm_forward_kernel(const KernelParams<T> P)
             }
         }
 
+        // ---- scaled recurrence: fold the constants ---------------------------------------------
+        // State kept per row r (gn = pGAPM of row r + 1, 1 below the last row; sigma_r = 1 on a
+        // group top, else pXX_r * sigma_{r-1}):
+        //     Xs = X / sigma_r            Ys = Y * gn            M as is
+        // so that  Z  = gn * (X + Y)                     = fma(Xs, gn * sigma_r, Ys)
+        //          M' = (M_d * pMM + Z_d) * e            (Z_d of the row above, previous column)
+        //          Ys'= M_l * (pMY * gn) + Ys_l * pYY
+        //          Xs'= M_u * (pMX / sigma_r) + Xs_u                       chained row: one FMA
+        //          Xs'= M_u * pMX + Xs_u * (pXX * sigma_{r-1})             group top
+        // Registers: pMM = pMM, pG = gn * sigma, pMX = pMX / sigma, pMY = pMY * gn, pXX = pYY,
+        // K2 = pXX * sigma_{r-1} of the group tops.  The last row's X sum is rescaled by `fin`.
+        // sigma >= pXX^3 (1e-3 at the usual GCP of Q10): an overflow of X / sigma makes the pair's
+        // sum non-finite, and emit_result hands such pairs to the bit-exact kernel.
+        V K2[NTOP];
+        V fin = O::splat((T)1);
+        if (SCALED) {
+            V gdn, sig[KH], sup;
+#pragma unroll
+            for (int c = 0; c < VL; ++c) {
+                const T v = __shfl_down_sync(FULL_MASK, O::get(pG[0], c), 1, LANES);
+                O::set(gdn, c, last_lane ? (T)1 : v);
+            }
+#pragma unroll
+            for (int p = 0; p < KH; ++p)
+#pragma unroll
+                for (int c = 0; c < VL; ++c)
+                    O::set(sig[p], c, (p % GRP == 0) ? (T)1 : O::get(pXX[p], c) * O::get(sig[p - (p % GRP ? 1 : 0)], c));
+            sup = O::shfl_up(sig[KH - 1], LANES);
+#pragma unroll
+            for (int p = 0; p < KH; ++p)
+#pragma unroll
+                for (int c = 0; c < VL; ++c) {
+                    const T gn = (p < KH - 1) ? O::get(pG[p < KH - 1 ? p + 1 : p], c) : O::get(gdn, c);
+                    const T s = O::get(sig[p], c);
+                    if (p % GRP == 0) {
+                        const T sprev = p ? O::get(sig[p ? p - 1 : 0], c) : O::get(sup, c);
+                        T k2 = O::get(pXX[p], c) * sprev;
+                        if (p == 0 && (dmask[c] & 1u)) k2 = zero;   // nothing above row 0 of the tile
+                        O::set(K2[p / GRP], c, k2);
+                    }
+                    O::set(pMX[p], c, S::div(O::get(pMX[p], c), s));
+                    O::set(pMY[p], c, O::get(pMY[p], c) * gn);
+                    O::set(pG[p], c, gn * s);
+                }
+            fin = sig[KH - 1];
+        }
+
         // ---- state: column-0 boundary -------------------------------------------------------
         int jh = 0;
         V M[KH], X[KH], Y[KH];
@@ -328,7 +384,8 @@ phmm_forward_kernel(const KernelParams<T> P)
             for (int p = 0; p < KH; ++p) {
                 M[p] = O::splat(zero); X[p] = O::splat(zero);
 #pragma unroll
-                for (int c = 0; c < VL; ++c) O::set(Y[p], c, ((dmask[c] >> p) & 1) ? iy : zero);
+                for (int c = 0; c < VL; ++c)
+                    O::set(Y[p], c, ((dmask[c] >> p) & 1) ? (SCALED ? iy * O::get(pG[p], c) : iy) : zero);
             }
         }
         V U1m = O::splat(zero), U1x = O::splat(zero), U1y = O::splat(zero);
@@ -386,9 +443,16 @@ phmm_forward_kernel(const KernelParams<T> P)
 #pragma unroll
                     for (int p = 0; p < KH; ++p) e[p] = O::lds(eaddr + p * N_CODES * 256);
                     // -- neighbours: bottom row of the upstream lane, one and two steps ago
+                    //    (scaled recurrence: U*y carries Z = gn * (X + Y) of that row)
                     U2m = U1m; U2x = U1x; U2y = U1y;
-                    U1m = O::shfl_up(M[KH - 1], LANES); U1x = O::shfl_up(X[KH - 1], LANES);
-                    U1y = O::shfl_up(Y[KH - 1], LANES);
+                    if (SCALED) {
+                        const V zb = O::fma(X[KH - 1], pG[KH - 1], Y[KH - 1]);
+                        U1m = O::shfl_up(M[KH - 1], LANES); U1x = O::shfl_up(X[KH - 1], LANES);
+                        U1y = O::shfl_up(zb, LANES);
+                    } else {
+                        U1m = O::shfl_up(M[KH - 1], LANES); U1x = O::shfl_up(X[KH - 1], LANES);
+                        U1y = O::shfl_up(Y[KH - 1], LANES);
+                    }
                     if (LONG && pass > 0 && gl == 0) {      // first row of a later block: "up" is the
                         U1m = sp_m; U1x = sp_x; U1y = sp_y; // block above
                         const int idx = min(max(s0 + k - a + 2, 0), ncols);
@@ -397,27 +461,44 @@ phmm_forward_kernel(const KernelParams<T> P)
                     }
                     // -- cell updates (computeMXY :183-198)
                     V nM[KH], nX[KH], nY[KH];
+                    if (SCALED) {
 #pragma unroll
-                    for (int p = 0; p < KH; ++p) {
-                        const V dm = p ? M[p - 1] : U2m;
-                        const V dx = p ? X[p - 1] : U2x;
-                        const V dy = p ? Y[p - 1] : U2y;
-                        const V yy = p ? pXX[p] : pYY0;
-                        if (FAST) {
-                            nM[p] = O::mul(O::fma(dm, pMM[p], O::mul(O::add(dx, dy), pG[p])), e[p]);
-                            nY[p] = O::fma(M[p], pMY[p], O::mul(Y[p], yy));
-                        } else {
-                            nM[p] = O::mul(O::add(O::add(O::mul(dm, pMM[p]), O::mul(dx, pG[p])),
-                                                  O::mul(dy, pG[p])), e[p]);
-                            nY[p] = O::add(O::mul(M[p], pMY[p]), O::mul(Y[p], yy));
+                        for (int p = 0; p < KH; ++p) {
+                            const V dm = p ? M[p - 1] : U2m;
+                            const V dz = p ? O::fma(X[p ? p - 1 : 0], pG[p ? p - 1 : 0], Y[p ? p - 1 : 0]) : U2y;
+                            nM[p] = O::mul(O::fma(dm, pMM[p], dz), e[p]);
+                            nY[p] = O::fma(M[p], pMY[p], O::mul(Y[p], pXX[p]));
                         }
-                    }
 #pragma unroll
-                    for (int p = 0; p < KH; ++p) {
-                        const V um = p ? nM[p - 1] : U1m;
-                        const V ux = p ? nX[p - 1] : U1x;
-                        if (FAST) nX[p] = O::fma(ux, pXX[p], O::mul(um, pMX[p]));
-                        else      nX[p] = O::add(O::mul(um, pMX[p]), O::mul(ux, pXX[p]));
+                        for (int p = 0; p < KH; ++p) {
+                            const V um = p ? nM[p ? p - 1 : 0] : U1m;
+                            const V ux = p ? nX[p ? p - 1 : 0] : U1x;
+                            if (p % GRP == 0) nX[p] = O::fma(um, pMX[p], O::mul(ux, K2[p / GRP]));
+                            else              nX[p] = O::fma(um, pMX[p], ux);
+                        }
+                    } else {
+#pragma unroll
+                        for (int p = 0; p < KH; ++p) {
+                            const V dm = p ? M[p - 1] : U2m;
+                            const V dx = p ? X[p - 1] : U2x;
+                            const V dy = p ? Y[p - 1] : U2y;
+                            const V yy = p ? pXX[p] : pYY0;
+                            if (FAST) {
+                                nM[p] = O::mul(O::fma(dm, pMM[p], O::mul(O::add(dx, dy), pG[p])), e[p]);
+                                nY[p] = O::fma(M[p], pMY[p], O::mul(Y[p], yy));
+                            } else {
+                                nM[p] = O::mul(O::add(O::add(O::mul(dm, pMM[p]), O::mul(dx, pG[p])),
+                                                      O::mul(dy, pG[p])), e[p]);
+                                nY[p] = O::add(O::mul(M[p], pMY[p]), O::mul(Y[p], yy));
+                            }
+                        }
+#pragma unroll
+                        for (int p = 0; p < KH; ++p) {
+                            const V um = p ? nM[p - 1] : U1m;
+                            const V ux = p ? nX[p - 1] : U1x;
+                            if (FAST) nX[p] = O::fma(ux, pXX[p], O::mul(um, pMX[p]));
+                            else      nX[p] = O::add(O::mul(um, pMX[p]), O::mul(ux, pXX[p]));
+                        }
                     }
 #pragma unroll
                     for (int p = 0; p < KH; ++p) { M[p] = nM[p]; X[p] = nX[p]; Y[p] = nY[p]; }
@@ -444,7 +525,8 @@ phmm_forward_kernel(const KernelParams<T> P)
 #pragma unroll
                             for (int c = 0; c < VL; ++c)
                                 if (rid[c] >= 0) {
-                                    const T res = S::add(O::get(sumM, c), O::get(sumX, c));   // :342
+                                    const T res = SCALED ? O::get(sumM, c) + O::get(sumX, c) * O::get(fin, c)
+                                                         : S::add(O::get(sumM, c), O::get(sumX, c));   // :342
                                     emit_result<FAST>(P, res, out_base[c] + out0 + jh, stream_off + hapstart, hl,
                                                       hap0 + jh, out0 + jh, rid[c], R[c]);
                                 }
@@ -456,7 +538,8 @@ phmm_forward_kernel(const KernelParams<T> P)
 #pragma unroll
                         for (int p = 0; p < KH; ++p)
 #pragma unroll
-                            for (int c = 0; c < VL; ++c) O::set(Y[p], c, ((dmask[c] >> p) & 1) ? iy : zero);
+                            for (int c = 0; c < VL; ++c)
+                                O::set(Y[p], c, ((dmask[c] >> p) & 1) ? (SCALED ? iy * O::get(pG[p], c) : iy) : zero);
                     }
                 }
             }

@@ -169,6 +169,42 @@ def test_fast_kernel_keeps_the_rescue_set_near_the_threshold():
     assert st["n_guard"] >= int(near.sum())
 
 
+def test_fast_kernel_with_exotic_gap_penalties():
+    """The fast FP32 kernel runs a rescaled recurrence (X / prod(pXX) inside groups of up to four rows);
+    gap-continuation and gap-open qualities far from GATK's constants make that scale tiny or the gap
+    terms large.  Overflowing pairs must come back through the bit-exact kernel, everything else stay
+    inside the FP32 bar, and the rescue set stay identical."""
+    rng = np.random.default_rng(7)
+    guard_total = 0
+    for case in range(4):
+        fb = synth.generic(700 + case, 6, (4, 12), (2, 6), (20, 250), (30, 400), q_rng=(6, 45), subst=0.03,
+                           foreign_frac=0.1)
+        n = fb.c.size
+        if case == 0:      # GCP anywhere in the Phred range, incl. 0 (pGAPM = 0) and very high
+            fb.c[:] = rng.integers(0, 94, n)
+        elif case == 1:    # high constant GCP: scale 1e-12 per group
+            fb.c[:] = 40
+            fb.i[:] = rng.integers(0, 10, n)
+            fb.d[:] = rng.integers(0, 10, n)
+        elif case == 2:    # cheap gaps everywhere
+            fb.c[:] = rng.integers(1, 6, n)
+            fb.i[:] = rng.integers(0, 46, n)
+            fb.d[:] = rng.integers(0, 46, n)
+        else:              # unmasked bytes: the kernel masks qualities with & 127 (:110-112,125)
+            fb.c[:] = rng.integers(0, 256, n)
+            fb.i[:] = rng.integers(0, 256, n)
+            fb.d[:] = rng.integers(0, 256, n)
+        ref = oracle.run_port(fb)
+        res, st = run(fb, fast=True)
+        check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, False, True)
+        guard_total += st["n_guard"]
+        eng = phmm.PairHMM(precision=phmm.FLOAT_ONLY, fast=True)
+        out = eng.compute(fb)
+        eng.close()
+        assert same_or_close(out, oracle.run_port(fb, mode=1).out, RTOL_FP32)
+    assert guard_total > 0      # at least one case must have exercised the overflow path
+
+
 def test_full_size_properties():
     """BASELINE config 2 at full size (2 M pairs): size-independent checks instead of the oracle."""
     fb = synth.c2_large()
