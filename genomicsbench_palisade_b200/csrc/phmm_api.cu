@@ -24,6 +24,11 @@ struct phmm_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    // class kernels of one phase run on side streams so that the tail of one persistent kernel
+    // (SMs idling while its last tasks finish) is filled by the blocks of the next
+    static const int N_SIDE = 4;
+    cudaStream_t side[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     // device tables
     float *d_ph2pr_f = nullptr, *d_mm_f = nullptr;
@@ -32,6 +37,7 @@ struct phmm_ctx {
     // options
     int precision = 0, fp32_fast = 0, fp64_fast = 0, seg_cols = 0;
     int force_kh = 0, force_lanes = 0;
+    int no_hp = 0;     // PHMM_NO_HP=1: fast FP32 kernels in the two-reads packing (A/B measurements)
     std::string error;
     std::mutex mu;     // the legacy symbols may be entered from several OpenMP threads
 };
@@ -58,6 +64,8 @@ struct phmm_workload {
     int32_t *d_hap_len = nullptr;
     ReadRec *d_reads = nullptr;
     Task *d_tasks = nullptr;
+    HTask *d_htasks = nullptr;
+    int planned_hp = 0;               // the plan holds haplotype-pair tasks: needs the fast FP32 kernels
     Task *d_resc = nullptr, *d_guard = nullptr;
     int32_t *d_ints = nullptr;        // [0..63] queue heads, [64..] ntasks per class, resc/guard counts
     double *d_out = nullptr, *d_raw64 = nullptr;
@@ -106,6 +114,11 @@ namespace phmm {
 KernelF32 lookup_f32(const KClass &kc, bool fast)
 {
     if (kc.vl != 2) return nullptr;
+    if (kc.hp) {
+        if (!fast) return nullptr;
+        return kc.lanes == 32 ? lookup_f32_hp_l32(kc.kh) : kc.lanes == 16 ? lookup_f32_hp_l16(kc.kh)
+             : kc.lanes == 8 ? lookup_f32_hp_l8(kc.kh) : nullptr;
+    }
     if (kc.longr) return lookup_f32_long(fast);
     switch (kc.lanes) {
     case 32: return fast ? lookup_f32_l32_f1(kc.kh) : lookup_f32_l32_f0(kc.kh);
@@ -161,6 +174,7 @@ extern "C" int phmm_create(int device, phmm_ctx **out)
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
     if (const char *s = getenv("PHMM_FORCE_CLASS")) sscanf(s, "%d,%d", &ctx->force_kh, &ctx->force_lanes);
+    if (const char *s = getenv("PHMM_NO_HP")) ctx->no_hp = atoi(s);
     auto bail = [&](const char *what, cudaError_t err) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
         phmm_destroy(ctx);
@@ -170,6 +184,11 @@ extern "C" int phmm_create(int device, phmm_ctx **out)
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     for (int k = 0; k < 4; ++k)
         if ((e = cudaEventCreate(&ctx->ev[k])) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    for (int k = 0; k < phmm_ctx::N_SIDE; ++k) {
+        if ((e = cudaStreamCreateWithFlags(&ctx->side[k], cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+        if ((e = cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    }
     const HostTables &t = host_tables();
     if ((e = cudaMalloc(&ctx->d_ph2pr_f, 128 * sizeof(float))) != cudaSuccess) return bail("cudaMalloc", e);
     if ((e = cudaMalloc(&ctx->d_ph2pr_d, 128 * sizeof(double))) != cudaSuccess) return bail("cudaMalloc", e);
@@ -191,6 +210,11 @@ extern "C" int phmm_destroy(phmm_ctx *ctx)
     cudaFree(ctx->d_ph2pr_f); cudaFree(ctx->d_ph2pr_d); cudaFree(ctx->d_mm_f); cudaFree(ctx->d_mm_d);
     cudaFree(ctx->d_bench);
     for (int k = 0; k < 4; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    for (int k = 0; k < phmm_ctx::N_SIDE; ++k) {
+        if (ctx->ev_join[k]) cudaEventDestroy(ctx->ev_join[k]);
+        if (ctx->side[k]) cudaStreamDestroy(ctx->side[k]);
+    }
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PHMM_OK;
@@ -248,6 +272,7 @@ static PlanOptions plan_options(const phmm_ctx *ctx)
     o.force_kh = ctx->force_kh;
     o.force_lanes = ctx->force_lanes;
     o.resident_warps = ctx->sm_count * 16;
+    o.hp = (ctx->fp32_fast && ctx->precision != 2 && !ctx->no_hp) ? 1 : 0;
     return o;
 }
 
@@ -256,7 +281,7 @@ extern "C" int phmm_workload_destroy(phmm_workload *w)
     if (!w) return PHMM_OK;
     if (w->ctx) cudaSetDevice(w->ctx->device);
     cudaFree(w->d_pool); cudaFree(w->d_stream); cudaFree(w->d_hap_len); cudaFree(w->d_reads);
-    cudaFree(w->d_tasks); cudaFree(w->d_resc); cudaFree(w->d_guard); cudaFree(w->d_ints);
+    cudaFree(w->d_tasks); cudaFree(w->d_htasks); cudaFree(w->d_resc); cudaFree(w->d_guard); cudaFree(w->d_ints);
     cudaFree(w->d_out); cudaFree(w->d_raw64); cudaFree(w->d_raw32); cudaFree(w->d_rescued);
     cudaFree(w->d_scratch);
     delete w;
@@ -294,13 +319,14 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
 
     const int64_t pool_len = P.pool_hi - P.pool_lo;
     w->pool_stride = (pool_len + 255) & ~(int64_t)255;
-    int64_t ntasks = 0;
+    int64_t ntasks = 0, nhtasks = 0;
     for (auto &cp : P.classes) {
         ClassDev cd;
         cd.kc = cp.kc;
-        cd.task_off = ntasks;
-        cd.ntasks = (int32_t)cp.tasks.size();
-        ntasks += (int64_t)cp.tasks.size();
+        cd.task_off = cp.kc.hp ? nhtasks : ntasks;
+        cd.ntasks = (int32_t)cp.ntasks();
+        (cp.kc.hp ? nhtasks : ntasks) += (int64_t)cp.ntasks();
+        if (cp.kc.hp) w->planned_hp = 1;
         w->classes.push_back(cd);
     }
 #define WL_ALLOC(ptr, n)                                             \
@@ -310,6 +336,7 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
     WL_ALLOC(w->d_hap_len, P.hap_len.size());
     WL_ALLOC(w->d_reads, P.reads.size());
     WL_ALLOC(w->d_tasks, ntasks);
+    WL_ALLOC(w->d_htasks, nhtasks);
     WL_ALLOC(w->d_ints, INTS_TOTAL);
     WL_ALLOC(w->d_out, P.n_pairs);
     WL_ALLOC(w->d_raw32, P.n_pairs);
@@ -319,7 +346,7 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
         WL_ALLOC(w->d_resc, tot);
         WL_ALLOC(w->d_guard, tot);
     }
-    if (P.long_max_cols > 0) {
+    if (P.long_max_cols > 0 || P.resc_cap[0] > 0) {     // resc_cap[0]: reads whose rescue / guard class is the multi-pass kernel
         // long reads may also come back as single-haplotype rescue / guard tasks
         const int64_t cols = std::max<int64_t>(P.long_max_cols, P.max_haplen + SEP_COLS) + 64;
         w->scratch_stride = 6 * cols;
@@ -350,7 +377,10 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
         if (!P.classes[c].tasks.empty())
             WL_TRY(cudaMemcpyAsync(w->d_tasks + w->classes[c].task_off, P.classes[c].tasks.data(),
                                    P.classes[c].tasks.size() * sizeof(Task), cudaMemcpyHostToDevice, st));
-        h2d += (int64_t)P.classes[c].tasks.size() * sizeof(Task);
+        if (!P.classes[c].htasks.empty())
+            WL_TRY(cudaMemcpyAsync(w->d_htasks + w->classes[c].task_off, P.classes[c].htasks.data(),
+                                   P.classes[c].htasks.size() * sizeof(HTask), cudaMemcpyHostToDevice, st));
+        h2d += (int64_t)P.classes[c].tasks.size() * sizeof(Task) + (int64_t)P.classes[c].htasks.size() * sizeof(HTask);
         ints[INTS_NTASKS + c] = w->classes[c].ntasks;
     }
     WL_TRY(cudaMemcpyAsync(w->d_ints, ints.data(), INTS_TOTAL * sizeof(int32_t), cudaMemcpyHostToDevice, st));
@@ -361,7 +391,7 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
     w->h2d_bytes = h2d;
     // host copies of the bulky plan parts are no longer needed
     std::vector<uint8_t>().swap(P.stream);
-    for (auto &cp : P.classes) std::vector<Task>().swap(cp.tasks);
+    for (auto &cp : P.classes) { std::vector<Task>().swap(cp.tasks); std::vector<HTask>().swap(cp.htasks); }
     *out = w;
     return PHMM_OK;
 }
@@ -376,6 +406,10 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
     const bool fast32 = ctx->fp32_fast != 0, fast64 = ctx->fp64_fast != 0;
     const int mode = w->precision;
     int launches = 0;
+    if (w->planned_hp && !fast32) {
+        ctx->error = "workload was planned for the fast FP32 kernels; PHMM_OPT_FP32_KERNEL changed since";
+        return PHMM_ERR_ARG;
+    }
 
     // queue heads and list counters back to zero
     CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_COUNTER, 0, 64 * sizeof(int32_t), st));
@@ -413,8 +447,8 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
 
     // dynamic shared memory (emission table + stream ring + run table per warp) and a grid that
     // fills the device once: the kernels are persistent, warps pull tasks from the queue
-    auto prepare = [&](const void *kernel, int kh, int64_t ntasks, bool longr, int *grid, int *smem) -> bool {
-        *smem = WARPS_PER_BLOCK * smem_per_warp(kh);
+    auto prepare = [&](const void *kernel, int kh, int64_t ntasks, bool longr, int *grid, int *smem, bool hp = false) -> bool {
+        *smem = WARPS_PER_BLOCK * (hp ? smem_per_warp_hp(kh) : smem_per_warp(kh));
         if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, *smem) != cudaSuccess) return false;
         int nb = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, WARPS_PER_BLOCK * 32, *smem) != cudaSuccess || nb < 1) nb = 1;
@@ -425,13 +459,42 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
         return true;
     };
     int counter_slot = 0, grid = 0, smem = 0;
+    // fork: the side streams wait for everything queued on the main stream so far;
+    // join: the main stream waits for the side streams that were used
+    int n_forked = 0;
+    auto fork = [&]() -> cudaError_t {
+        n_forked = 0;
+        return cudaEventRecord(ctx->ev_fork, st);
+    };
+    auto side_stream = [&](cudaStream_t *out) -> cudaError_t {
+        const int k = n_forked % phmm_ctx::N_SIDE;
+        if (n_forked < phmm_ctx::N_SIDE) {
+            cudaError_t e = cudaStreamWaitEvent(ctx->side[k], ctx->ev_fork, 0);
+            if (e != cudaSuccess) return e;
+        }
+        ++n_forked;
+        *out = ctx->side[k];
+        return cudaSuccess;
+    };
+    auto join = [&]() -> cudaError_t {
+        for (int k = 0; k < std::min(n_forked, (int)phmm_ctx::N_SIDE); ++k) {
+            cudaError_t e = cudaEventRecord(ctx->ev_join[k], ctx->side[k]);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(st, ctx->ev_join[k], 0);
+            if (e != cudaSuccess) return e;
+        }
+        n_forked = 0;
+        return cudaSuccess;
+    };
+    cudaStream_t ks = st;
 
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev[0], st));
     // ---- main pass over the planned tasks ---------------------------------------------------
+    CUDA_TRY(ctx, fork());
     for (size_t c = 0; c < w->classes.size(); ++c) {
         const ClassDev &cd = w->classes[c];
         if (cd.ntasks == 0) continue;
         if (counter_slot >= 60) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
+        CUDA_TRY(ctx, side_stream(&ks));
         if (mode == 2) {
             KernelF64 k = cd.kc.longr ? lookup_f64_long(fast64) : lookup_f64(cd.kc.kh, fast64);
             if (!k || cd.kc.vl != 1 || cd.kc.lanes != 32) { ctx->error = "no FP64 kernel for class"; return PHMM_ERR_ARG; }
@@ -439,48 +502,56 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
             pd.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
             pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
             if (!prepare((const void *)k, cd.kc.kh, cd.ntasks, cd.kc.longr, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
-            k<<<grid, WARPS_PER_BLOCK * 32, smem, st>>>(pd);
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, ks>>>(pd);
         } else {
             KernelF32 k = lookup_f32(cd.kc, fast32);
             if (!k) { ctx->error = "no FP32 kernel for class"; return PHMM_ERR_ARG; }
-            pf.tasks = w->d_tasks + cd.task_off;
+            pf.tasks = cd.kc.hp ? nullptr : w->d_tasks + cd.task_off;
+            pf.htasks = cd.kc.hp ? w->d_htasks + cd.task_off : nullptr;
             pf.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
             pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
-            if (!prepare((const void *)k, cd.kc.kh, cd.ntasks, cd.kc.longr, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
-            k<<<grid, WARPS_PER_BLOCK * 32, smem, st>>>(pf);
+            if (!prepare((const void *)k, cd.kc.kh, cd.ntasks, cd.kc.longr, &grid, &smem, cd.kc.hp != 0)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, ks>>>(pf);
         }
         CUDA_TRY(ctx, cudaGetLastError());
         ++launches;
     }
+    CUDA_TRY(ctx, join());
     // ---- fast kernel only: near-threshold and non-finite sums re-decided by the bit-exact kernel ----
     if (mode != 2 && fast32) {
+        CUDA_TRY(ctx, fork());
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (w->resc_cap[kh] == 0) continue;
+            CUDA_TRY(ctx, side_stream(&ks));
             KernelF32 k = kh ? lookup_f32_l32_f0(kh) : lookup_f32_long(false);
             pf.tasks = w->d_guard + w->resc_off[kh];
             pf.ntasks_ptr = w->d_ints + INTS_GUARD + kh;
             pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
             // the exact kernel never takes the guard branch (FAST = false)
             if (!prepare((const void *)k, kh ? kh : LONG_KH, std::min<int64_t>(w->resc_cap[kh], 4096), kh == 0, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
-            k<<<grid, WARPS_PER_BLOCK * 32, smem, st>>>(pf);
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, ks>>>(pf);
             CUDA_TRY(ctx, cudaGetLastError());
             ++launches;
         }
+        CUDA_TRY(ctx, join());
     }
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev[1], st));
     // ---- FP64 rescue (IntelPairHmmCSource.cpp:73-75) --------------------------------------------
     if (mode == 0) {
+        CUDA_TRY(ctx, fork());
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (w->resc_cap[kh] == 0) continue;
+            CUDA_TRY(ctx, side_stream(&ks));
             KernelF64 k = kh ? lookup_f64(kh, fast64) : lookup_f64_long(fast64);
             pd.tasks = w->d_resc + w->resc_off[kh];
             pd.ntasks_ptr = w->d_ints + INTS_RESC + kh;
             pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
             if (!prepare((const void *)k, kh ? kh : LONG_KH, w->resc_cap[kh], kh == 0, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
-            k<<<grid, WARPS_PER_BLOCK * 32, smem, st>>>(pd);
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, ks>>>(pd);
             CUDA_TRY(ctx, cudaGetLastError());
             ++launches;
         }
+        CUDA_TRY(ctx, join());
     }
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev[2], st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
@@ -734,7 +805,8 @@ extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int
 {
     if (!fb || !info) return PHMM_ERR_ARG;
     PlanOptions o;
-    o.precision = precision;
+    o.precision = precision & 0xff;
+    o.hp = (precision >> 8) & 1;          // plan for the fast FP32 (haplotype-pair) kernels
     o.seg_cols = seg_cols;
     Plan P;
     std::string err;
@@ -747,12 +819,26 @@ extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int
         info[8 + 4 * c + 0] = P.classes[c].kc.kh;
         info[8 + 4 * c + 1] = P.classes[c].kc.lanes;
         info[8 + 4 * c + 2] = P.classes[c].kc.vl;
-        info[8 + 4 * c + 3] = (int64_t)P.classes[c].tasks.size();
+        info[8 + 4 * c + 3] = (int64_t)P.classes[c].ntasks();
     }
-    for (auto &cp : P.classes) ntasks += (int64_t)cp.tasks.size();
+    for (auto &cp : P.classes) ntasks += (int64_t)cp.ntasks();
     info[6] = ntasks;
     if (pair_cover) {
         // walk every task the way the kernel does and count how often each pair is produced
+        for (auto &cp : P.classes)
+            for (auto &t : cp.htasks)
+                for (int h = 0; h < 2; ++h) {
+                    const int nh = t.nh[h];
+                    int64_t cols = 0;
+                    for (int j = 0; j < nh; ++j) cols += P.hap_len[t.hap0[h] + j] + SEP_COLS;
+                    if (cols != t.ncols[h] || nh > MAX_RUN_HAPS || !cp.kc.hp) return PHMM_ERR_ARG;
+                    for (int g = 0; g < cp.kc.group(); ++g) {
+                        if (t.read[g] < 0) continue;
+                        const ReadRec &rr = P.reads[t.read[g]];
+                        if (rr.len > cp.kc.capacity()) return PHMM_ERR_ARG;
+                        for (int j = 0; j < nh; ++j) pair_cover[rr.out_base + t.out0[h] + j]++;
+                    }
+                }
         for (auto &cp : P.classes)
             for (auto &t : cp.tasks) {
                 const int nh = t.nh;

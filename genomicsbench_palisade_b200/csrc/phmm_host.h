@@ -31,11 +31,14 @@ struct PlanOptions {
     int seg_cols = 0;         // 0 = adaptive
     int resident_warps = 2368;   // warps the device keeps in flight (for adaptive run sizing)
     int force_kh = 0, force_lanes = 0;   // debugging / benchmarking: pin the kernel class
+    int hp = 0;               // 1 = plan haplotype-pair tasks (fast FP32 kernels) for single-pass reads
 };
 
 struct ClassPlan {
     KClass kc;
     std::vector<Task> tasks;   // sorted by decreasing cost
+    std::vector<HTask> htasks; // haplotype-pair classes (kc.hp) use these instead
+    size_t ntasks() const { return kc.hp ? htasks.size() : tasks.size(); }
     int64_t cells = 0;
     int64_t pairs = 0;
 };
@@ -64,6 +67,9 @@ KernelF32 lookup_f32_l32_f0(int kh);
 KernelF32 lookup_f32_l32_f1(int kh);
 KernelF32 lookup_f32_l16_f0(int kh);
 KernelF32 lookup_f32_l16_f1(int kh);
+KernelF32 lookup_f32_hp_l32(int kh);
+KernelF32 lookup_f32_hp_l16(int kh);
+KernelF32 lookup_f32_hp_l8(int kh);
 KernelF64 lookup_f64_f0(int kh);
 KernelF64 lookup_f64_f1(int kh);
 KernelF32 lookup_f32(const KClass &kc, bool fast);

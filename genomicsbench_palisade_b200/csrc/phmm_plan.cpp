@@ -18,17 +18,28 @@ namespace phmm {
 bool choose_class(int rslen, const PlanOptions &opt, KClass *out)
 {
     const int vl = opt.precision == 2 ? 1 : 2;
+    const bool hp = opt.hp && opt.precision != 2;
+    const int rows = rslen + 1;                // + the dummy row that carries DP row 0
     if (opt.force_kh > 0 && opt.force_lanes > 0) {
-        KClass kc{opt.force_kh, opt.precision == 2 ? 32 : opt.force_lanes, vl, 0};
-        if (kc.capacity() >= rslen) { *out = kc; return true; }
+        KClass kc{opt.force_kh, opt.precision == 2 ? 32 : opt.force_lanes, vl, 0, hp ? 1 : 0};
+        const bool ok = hp ? (kc.kh <= MAX_KH_HP && (kc.lanes == 32 || kc.lanes == 16 || kc.lanes == 8))
+                           : (kc.kh <= MAX_KH && (kc.lanes == 32 || (kc.lanes == 16 && vl == 2)));
+        if (ok && kc.capacity() >= rslen) { *out = kc; return true; }
+    }
+    if (hp) {
+        // Haplotype-pair kernels: the tallest register tile that fits wins (fewest lanes: least
+        // wavefront fill, shuffles and sums amortised over the most rows).
+        for (int lanes = 8; lanes <= 32; lanes *= 2)
+            if (rows <= lanes * MAX_KH_HP) { *out = KClass{(rows + lanes - 1) / lanes, lanes, 2, 0, 1}; return true; }
+        *out = KClass{LONG_KH, 32, 2, 1, 0};
+        return true;
     }
     // Fewest padded rows wins; the register-file-bound cell update costs the same per row in
     // every class.  16 lanes (two read pairs per warp, half the wavefront fill) for rows that fit,
     // 32 lanes above; FP64 always 32 lanes.
-    const int rows = rslen + 1;                // + the dummy row that carries DP row 0
-    if (vl == 2 && rows <= 16 * MAX_KH) { *out = KClass{(rows + 15) / 16, 16, vl, 0}; return true; }
-    if (rows <= 32 * MAX_KH) { *out = KClass{(rows + 31) / 32, 32, vl, 0}; return true; }
-    *out = KClass{LONG_KH, 32, vl, 1};         // longer than every single-pass class: multi-pass
+    if (vl == 2 && rows <= 16 * MAX_KH) { *out = KClass{(rows + 15) / 16, 16, vl, 0, 0}; return true; }
+    if (rows <= 32 * MAX_KH) { *out = KClass{(rows + 31) / 32, 32, vl, 0, 0}; return true; }
+    *out = KClass{LONG_KH, 32, vl, 1, 0};      // longer than every single-pass class: multi-pass
     return true;
 }
 
@@ -97,147 +108,241 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
         hap_col[fb.n_haps] = total;
         P.stream.assign((size_t)total + STREAM_SLACK, 0);
         P.hap_len.assign((size_t)fb.n_haps + 1, 1);
+        uint8_t code_lut[256];
+        for (int v = 0; v < 256; ++v) code_lut[v] = base_code((uint8_t)v);
         for (h = 0; h < fb.n_haps; ++h) {
             const uint8_t *src = fb.hap + fb.hap_off[h];
             uint8_t *dst = P.stream.data() + hap_col[h];
             const int len = fb.hap_len[h];
-            for (int k = 0; k < len; ++k) dst[k] = base_code(src[k]);
+            for (int k = 0; k < len; ++k) dst[k] = code_lut[src[k]];
             P.hap_len[h] = len;
         }
     }
 
-    // ---- reads, classes, tasks -----------------------------------------------------------------
+    // ---- reads, classes -----------------------------------------------------------------------
     P.reads.resize((size_t)fb.n_reads);
-    struct ClassKey { int kh, lanes, vl; };
     auto class_index = [&](const KClass &kc) -> int {
-        for (size_t k = 0; k < P.classes.size(); ++k)
-            if (P.classes[k].kc.kh == kc.kh && P.classes[k].kc.lanes == kc.lanes && P.classes[k].kc.vl == kc.vl &&
-                P.classes[k].kc.longr == kc.longr)
-                return (int)k;
+        for (size_t k = 0; k < P.classes.size(); ++k) {
+            const KClass &o = P.classes[k].kc;
+            if (o.kh == kc.kh && o.lanes == kc.lanes && o.vl == kc.vl && o.longr == kc.longr && o.hp == kc.hp) return (int)k;
+        }
         ClassPlan cp;
         cp.kc = kc;
         P.classes.push_back(cp);
         return (int)P.classes.size() - 1;
     };
-
-    // adaptive run length: aim at >= 3 tasks per resident warp, but keep runs long enough that
-    // the wavefront fill (<= 63 steps) stays small
-    int seg_cols = opt.seg_cols > 0 ? opt.seg_cols : 4096;
     std::vector<int> read_class((size_t)fb.n_reads);
     {
-        int64_t r = 0;
-        for (int64_t b = 0; b < fb.n_batches; ++b)
-            for (int k = 0; k < fb.batch_num_reads[b]; ++k, ++r) {
-                KClass kc;
-                if (!choose_class(fb.read_len[r], opt, &kc)) {
-                    snprintf(msg, sizeof msg, "read %lld of length %d exceeds the largest single-pass kernel class",
-                             (long long)r, fb.read_len[r]);
-                    return fail(PHMM_ERR_TOO_LONG, msg);
-                }
-                read_class[r] = class_index(kc);
+        int class_of_len[512];                 // memo for the common lengths
+        for (int &v : class_of_len) v = -1;
+        for (int64_t r = 0; r < fb.n_reads; ++r) {
+            const int len = fb.read_len[r];
+            if (len < 512 && class_of_len[len] >= 0) { read_class[r] = class_of_len[len]; continue; }
+            KClass kc;
+            if (!choose_class(len, opt, &kc)) {
+                snprintf(msg, sizeof msg, "read %lld of length %d exceeds the largest kernel class", (long long)r, len);
+                return fail(PHMM_ERR_TOO_LONG, msg);
             }
+            read_class[r] = class_index(kc);
+            if (len < 512) class_of_len[len] = read_class[r];
+        }
     }
-    auto count_tasks = [&](int cols) -> int64_t {
-        int64_t n = 0, r0 = 0, h0 = 0;
-        std::vector<int64_t> per_class(P.classes.size());
+    const size_t ncls = P.classes.size();
+
+    // ---- per batch: reads by class --------------------------------------------------------------
+    // rl[b * ncls + c] = reads of batch b handled by class c.  A class's leftover reads (fewer
+    // than one full task) move up to the next larger class of the batch, where they fill slots
+    // instead of leaving part of a warp idle.
+    struct BatchInfo { int64_t r0, h0, out0, cols; };
+    std::vector<BatchInfo> binfo((size_t)fb.n_batches);
+    std::vector<std::vector<int32_t>> rl((size_t)fb.n_batches * ncls);
+    std::vector<int> order(ncls);
+    for (size_t c = 0; c < ncls; ++c) order[c] = (int)c;
+    std::sort(order.begin(), order.end(), [&](int x, int y) {
+        const KClass &kx = P.classes[x].kc, &ky = P.classes[y].kc;
+        if (kx.longr != ky.longr) return kx.longr < ky.longr;
+        return kx.capacity() < ky.capacity();
+    });
+    {
+        int64_t r0 = 0, h0 = 0, out0 = 0;
         for (int64_t b = 0; b < fb.n_batches; ++b) {
             const int bnr = fb.batch_num_reads[b], bnh = fb.batch_num_haps[b];
-            int64_t runs = 0, acc = 0;
-            for (int k = 0, n_in = 0; k < bnh; ++k) {
-                acc += fb.hap_len[h0 + k] + SEP_COLS;
-                if (acc >= cols || ++n_in >= MAX_RUN_HAPS || k == bnh - 1) { ++runs; acc = 0; n_in = 0; }
+            int64_t sum_h = 0;
+            for (int k = 0; k < bnh; ++k) sum_h += fb.hap_len[h0 + k];
+            binfo[b] = BatchInfo{r0, h0, out0, sum_h + (int64_t)bnh * SEP_COLS};
+            std::vector<int32_t> *by_class = &rl[(size_t)b * ncls];
+            for (int k = 0; k < bnr; ++k) {
+                const int64_t r = r0 + k;
+                ReadRec &rr = P.reads[r];
+                rr.off = fb.read_off[r] - P.pool_lo;
+                rr.len = fb.read_len[r];
+                rr.batch = (int32_t)b;
+                rr.out_base = out0 + (int64_t)k * bnh;
+                by_class[read_class[r]].push_back((int32_t)r);
+                P.n_cells += (int64_t)rr.len * sum_h;
+                P.resc_cap[scalar_class_of(rr.len)] += bnh;
             }
-            std::fill(per_class.begin(), per_class.end(), 0);
-            for (int k = 0; k < bnr; ++k) per_class[read_class[r0 + k]]++;
-            for (size_t c = 0; c < P.classes.size(); ++c) {
-                const int g = P.classes[c].kc.group();
-                n += runs * ((per_class[c] + g - 1) / g);
+            int prev = -1;
+            for (size_t oi = 0; oi < ncls; ++oi) {
+                const int c = order[oi];
+                if (by_class[c].empty()) continue;
+                if (prev >= 0 && P.classes[prev].kc.longr == P.classes[c].kc.longr) {
+                    std::vector<int32_t> &src = by_class[prev], &dst = by_class[c];
+                    const size_t rem = src.size() % (size_t)P.classes[prev].kc.group();
+                    for (size_t j = 0; j < rem; ++j) { dst.push_back(src.back()); src.pop_back(); }
+                }
+                prev = c;
             }
+            if (bnh > 0)
+                for (size_t c = 0; c < ncls; ++c)
+                    for (int32_t r : by_class[c]) {
+                        P.classes[c].cells += (int64_t)P.reads[r].len * sum_h;
+                        P.classes[c].pairs += bnh;
+                    }
+            P.n_pairs += (int64_t)bnr * bnh;
+            out0 += (int64_t)bnr * bnh;
             r0 += bnr;
             h0 += bnh;
         }
+    }
+
+    // ---- runs of consecutive haplotypes -----------------------------------------------------------
+    // A batch's haplotypes are cut into n contiguous runs of about `cols` columns each (n even for
+    // the haplotype-pair classes, which take two runs per task), balanced so that the two runs of a
+    // pair end within half a haplotype of each other.
+    auto runs_of = [&](int64_t b, int cols, bool pair) -> int {
+        const int bnh = fb.batch_num_haps[b];
+        if (bnh == 0) return 0;
+        int64_t n = (binfo[b].cols + cols - 1) / cols;
+        n = std::max<int64_t>(n, (bnh + MAX_RUN_HAPS - 1) / MAX_RUN_HAPS);
+        if (pair) n = (n + 1) & ~(int64_t)1;
+        return (int)std::min<int64_t>(n, bnh);
+    };
+    auto count_tasks = [&](int cols) -> int64_t {
+        int64_t n = 0;
+        for (int64_t b = 0; b < fb.n_batches; ++b)
+            for (size_t c = 0; c < ncls; ++c) {
+                const KClass &kc = P.classes[c].kc;
+                const int64_t nr = (int64_t)rl[(size_t)b * ncls + c].size();
+                if (!nr) continue;
+                const int runs = runs_of(b, cols, kc.hp != 0);
+                n += (kc.hp ? (runs + 1) / 2 : runs) * ((nr + kc.group() - 1) / kc.group());
+            }
         return n;
     };
+    // adaptive run length: aim at >= 3 tasks per resident warp, but keep runs long enough that
+    // the wavefront fill (<= 31 steps) stays small
+    int seg_cols = opt.seg_cols > 0 ? opt.seg_cols : 4096;
     if (opt.seg_cols <= 0)
         while (seg_cols > 512 && count_tasks(seg_cols) < 3 * (int64_t)opt.resident_warps) seg_cols /= 2;
 
-    int64_t r0 = 0, h0 = 0, out0 = 0;
-    std::vector<std::vector<int32_t>> by_class(P.classes.size());
-    for (int64_t b = 0; b < fb.n_batches; ++b) {
-        const int bnr = fb.batch_num_reads[b], bnh = fb.batch_num_haps[b];
-        int64_t sum_h = 0;
-        for (int k = 0; k < bnh; ++k) sum_h += fb.hap_len[h0 + k];
-        for (auto &v : by_class) v.clear();
-        for (int k = 0; k < bnr; ++k) {
-            const int64_t r = r0 + k;
-            ReadRec &rr = P.reads[r];
-            rr.off = fb.read_off[r] - P.pool_lo;
-            rr.len = fb.read_len[r];
-            rr.batch = (int32_t)b;
-            rr.out_base = out0 + (int64_t)k * bnh;
-            by_class[read_class[r]].push_back((int32_t)r);
-            P.n_cells += (int64_t)rr.len * sum_h;
-            P.resc_cap[scalar_class_of(rr.len)] += bnh;
-        }
-        // a class's leftover reads (fewer than one full task) move up to the next larger class of
-        // the batch, where they fill slots instead of leaving half a warp idle
-        {
-            std::vector<int> order;
-            for (size_t c = 0; c < P.classes.size(); ++c)
-                if (!by_class[c].empty()) order.push_back((int)c);
-            std::sort(order.begin(), order.end(), [&](int x, int y) {
-                const KClass &kx = P.classes[x].kc, &ky = P.classes[y].kc;
-                if (kx.longr != ky.longr) return kx.longr < ky.longr;
-                return kx.capacity() < ky.capacity();
-            });
-            for (size_t oi = 0; oi + 1 < order.size(); ++oi) {
-                std::vector<int32_t> &src = by_class[order[oi]], &dst = by_class[order[oi + 1]];
-                const size_t rem = src.size() % (size_t)P.classes[order[oi]].kc.group();
-                for (size_t j = 0; j < rem; ++j) { dst.push_back(src.back()); src.pop_back(); }
-            }
-        }
-        if (bnh > 0)
-            for (size_t c = 0; c < P.classes.size(); ++c)
-                for (int32_t r : by_class[c]) {
-                    P.classes[c].cells += (int64_t)P.reads[r].len * sum_h;
-                    P.classes[c].pairs += bnh;
+    struct Run { int64_t b; int k0, k1; int32_t cols; };
+    std::vector<Run> runs[2];                  // [0] single runs (classic classes), [1] run pairs: 2j, 2j + 1
+    bool any_kind[2] = {false, false};
+    for (size_t c = 0; c < ncls; ++c) any_kind[P.classes[c].kc.hp ? 1 : 0] = true;
+    std::vector<int> cuts;
+    for (int kind = 0; kind < 2; ++kind) {
+        if (!any_kind[kind]) continue;
+        for (int64_t b = 0; b < fb.n_batches; ++b) {
+            const int bnh = fb.batch_num_haps[b];
+            if (bnh == 0) continue;
+            bool used = false;
+            for (size_t c = 0; c < ncls && !used; ++c)
+                used = (P.classes[c].kc.hp ? 1 : 0) == kind && !rl[(size_t)b * ncls + c].empty();
+            if (!used) continue;
+            const int64_t h0 = binfo[b].h0, total = binfo[b].cols;
+            int n = runs_of(b, seg_cols, kind == 1);
+            for (;;) {
+                cuts.assign(1, 0);
+                int64_t acc = 0;
+                int k = 0;
+                bool ok = true;
+                for (int j = 1; j <= n; ++j) {
+                    const int64_t target = total * j / n;
+                    const int kmax = bnh - (n - j);              // leave one haplotype per remaining run
+                    int k1 = k;
+                    while (k1 < kmax && (k1 == k || acc + (fb.hap_len[h0 + k1] + SEP_COLS) / 2 < target)) {
+                        acc += fb.hap_len[h0 + k1] + SEP_COLS;
+                        ++k1;
+                    }
+                    if (j == n) while (k1 < bnh) { acc += fb.hap_len[h0 + k1] + SEP_COLS; ++k1; }
+                    if (k1 - k > MAX_RUN_HAPS) ok = false;
+                    cuts.push_back(k1);
+                    k = k1;
                 }
-        // runs of consecutive haplotypes
-        int k = 0;
-        while (k < bnh) {
-            int k1 = k;
-            int64_t acc = 0;
-            while (k1 < bnh && acc < seg_cols && k1 - k < MAX_RUN_HAPS) { acc += fb.hap_len[h0 + k1] + SEP_COLS; ++k1; }
-            for (size_t c = 0; c < P.classes.size(); ++c) {
-                const std::vector<int32_t> &rl = by_class[c];
-                const int g = P.classes[c].kc.group();
-                for (size_t i = 0; i < rl.size(); i += g) {
-                    Task t;
-                    t.stream_off = hap_col[h0 + k];
-                    t.ncols = (int32_t)acc;
-                    t.hap0 = (int32_t)(h0 + k);
-                    t.out0 = k;
-                    for (int j = 0; j < MAX_GROUP; ++j)
-                        t.read[j] = (j < g && i + j < rl.size()) ? rl[i + j] : -1;
-                    t.nh = k1 - k;
-                    P.classes[c].tasks.push_back(t);
-                    if (P.classes[c].kc.longr) P.long_max_cols = std::max(P.long_max_cols, t.ncols);
-                }
+                if (ok || n >= bnh) break;
+                n = std::min(bnh, n + (kind == 1 ? 2 : 1));
             }
-            k = k1;
+            for (size_t j = 0; j + 1 < cuts.size(); ++j) {
+                int64_t w = 0;
+                for (int k = cuts[j]; k < cuts[j + 1]; ++k) w += fb.hap_len[h0 + k] + SEP_COLS;
+                runs[kind].push_back(Run{b, cuts[j], cuts[j + 1], (int32_t)w});
+            }
+            if (kind == 1 && (cuts.size() - 1) % 2 == 1) runs[1].push_back(Run{b, 0, 0, 0});   // idle second half
         }
-        P.n_pairs += (int64_t)bnr * bnh;
-        out0 += (int64_t)bnr * bnh;
-        r0 += bnr;
-        h0 += bnh;
     }
-    // longest first: the device-side queue then behaves like LPT list scheduling
-    for (auto &cp : P.classes)
-        std::stable_sort(cp.tasks.begin(), cp.tasks.end(),
-                         [](const Task &a, const Task &b) { return a.ncols > b.ncols; });
+
+    // ---- tasks, longest first: the device-side queue then behaves like LPT list scheduling ---------
+    {
+        std::vector<int32_t> idx(runs[0].size());
+        for (size_t j = 0; j < idx.size(); ++j) idx[j] = (int32_t)j;
+        std::stable_sort(idx.begin(), idx.end(), [&](int32_t x, int32_t y) { return runs[0][x].cols > runs[0][y].cols; });
+        for (int32_t j : idx) {
+            const Run &rn = runs[0][j];
+            const BatchInfo &bi = binfo[rn.b];
+            for (size_t c = 0; c < ncls; ++c) {
+                const KClass &kc = P.classes[c].kc;
+                if (kc.hp) continue;
+                const std::vector<int32_t> &v = rl[(size_t)rn.b * ncls + c];
+                const int g = kc.group();
+                for (size_t i = 0; i < v.size(); i += g) {
+                    Task t;
+                    t.stream_off = hap_col[bi.h0 + rn.k0];
+                    t.ncols = rn.cols;
+                    t.hap0 = (int32_t)(bi.h0 + rn.k0);
+                    t.out0 = rn.k0;
+                    for (int q = 0; q < MAX_GROUP; ++q) t.read[q] = (q < g && i + q < v.size()) ? v[i + q] : -1;
+                    t.nh = rn.k1 - rn.k0;
+                    P.classes[c].tasks.push_back(t);
+                    if (kc.longr) P.long_max_cols = std::max(P.long_max_cols, t.ncols);
+                }
+            }
+        }
+    }
+    {
+        const size_t npairs = runs[1].size() / 2;
+        std::vector<int32_t> idx(npairs);
+        for (size_t j = 0; j < npairs; ++j) idx[j] = (int32_t)j;
+        auto cost = [&](int32_t x) { return std::max(runs[1][2 * x].cols, runs[1][2 * x + 1].cols); };
+        std::stable_sort(idx.begin(), idx.end(), [&](int32_t x, int32_t y) { return cost(x) > cost(y); });
+        for (int32_t j : idx) {
+            const Run *rn = &runs[1][2 * (size_t)j];
+            const BatchInfo &bi = binfo[rn[0].b];
+            for (size_t c = 0; c < ncls; ++c) {
+                const KClass &kc = P.classes[c].kc;
+                if (!kc.hp) continue;
+                const std::vector<int32_t> &v = rl[(size_t)rn[0].b * ncls + c];
+                const int g = kc.group();
+                for (size_t i = 0; i < v.size(); i += g) {
+                    HTask t;
+                    memset(&t, 0, sizeof t);
+                    for (int h = 0; h < 2; ++h) {
+                        const bool idle = rn[h].k1 == rn[h].k0;
+                        t.stream_off[h] = hap_col[bi.h0 + (idle ? rn[0].k0 : rn[h].k0)];
+                        t.ncols[h] = rn[h].cols;
+                        t.hap0[h] = (int32_t)(bi.h0 + (idle ? rn[0].k0 : rn[h].k0));
+                        t.out0[h] = idle ? rn[0].k0 : rn[h].k0;
+                        t.nh[h] = (int16_t)(rn[h].k1 - rn[h].k0);
+                    }
+                    for (int q = 0; q < MAX_HP_GROUP; ++q) t.read[q] = (q < g && i + q < v.size()) ? v[i + q] : -1;
+                    P.classes[c].htasks.push_back(t);
+                }
+            }
+        }
+    }
     // drop classes that ended up empty (possible when a batch has no haplotypes)
     P.classes.erase(std::remove_if(P.classes.begin(), P.classes.end(),
-                                   [](const ClassPlan &c) { return c.tasks.empty(); }),
+                                   [](const ClassPlan &c) { return c.ntasks() == 0; }),
                     P.classes.end());
     return PHMM_OK;
 }

@@ -47,6 +47,21 @@ struct Task {
     int32_t nh;          // haplotypes in the run (<= MAX_RUN_HAPS)
 };
 
+// Unit of work of the fast FP32 "haplotype-pair" kernels: each lane group holds ONE read and
+// streams it against TWO runs of haplotypes at once, one in each half of the packed f32x2
+// registers.  Both halves then share every per-row constant, which FFMA2/FMUL2 take as a single
+// 32-bit broadcast operand (Rn.F32) instead of a register pair.
+static const int MAX_HP_GROUP = 4;
+struct HTask {
+    int64_t stream_off[2];   // first column of each run in the haplotype stream
+    int32_t ncols[2];        // columns incl. separators; 0 = half idle
+    int32_t hap0[2];         // first haplotype of each run (valid index even when idle)
+    int32_t out0[2];         // index of that haplotype within its batch
+    int16_t nh[2];           // haplotypes per run (<= MAX_RUN_HAPS)
+    int32_t read[MAX_HP_GROUP];   // ReadRec index per lane group, -1 = idle
+    int32_t pad_;
+};
+
 // Kernel class = how reads are laid over a warp.
 //   kh    rows per thread (register tile height)
 //   lanes threads per read (32 or 16); a warp works on 32/lanes lane groups at once
@@ -59,10 +74,12 @@ struct Task {
 //         the bottom row of a block travels to the next pass through an HBM scratch row
 //         (the reference does the same one level down with its shiftOut arrays,
 //         avx-pairhmm-template.h:224,265-297).
+//   hp    1 = haplotype-pair kernel (fast FP32 only): one read per lane group, vl counts the
+//         haplotype runs instead; lanes 32, 16 or 8, kh <= MAX_KH_HP
 struct KClass {
-    int kh, lanes, vl, longr;
+    int kh, lanes, vl, longr, hp;
     int capacity() const { return longr ? 0x7fffffff : kh * lanes - 1; }
-    int group() const { return (32 / lanes) * vl; }      // reads per task
+    int group() const { return hp ? 32 / lanes : (32 / lanes) * vl; }      // reads per task
 };
 
 static const int SEP_COLS = 4;                // separator columns after each haplotype (= columns per loop iteration)
@@ -72,12 +89,16 @@ static const int STREAM_RING = 2048;          // per-warp shared-memory ring (4 
 static const int STREAM_SLACK = 2 * STREAM_CHUNK + 128;   // readable bytes past the last column
 static const int WARPS_PER_BLOCK = 4;
 static const int MAX_KH = 8;                  // single-pass classes: kh <= 8 (255 rows at 32 lanes)
+static const int MAX_KH_HP = 16;              // haplotype-pair classes: kh <= 16 (511 rows at 32 lanes)
 static const int LONG_KH = 8;                 // register tile of the multi-pass kernels
 static const int MAX_KH_SCALAR = MAX_KH;      // FP64 rescue classes: 32 lanes x kh rows
 
 // dynamic shared memory per warp: emission table [kh][N_CODES][32 lanes] of 8 bytes, the stream
 // ring, and the per-run haplotype table (INITIAL_CONSTANT / haplen as 8 bytes + length)
 static inline int smem_per_warp(int kh) { return kh * N_CODES * 256 + STREAM_RING + (MAX_RUN_HAPS + 2) * 12; }
+// haplotype-pair kernels: emission table [kh][N_CODES][32 lanes] of 4 bytes, two stream rings, two
+// run tables (float INITIAL_CONSTANT / haplen + int length)
+static inline int smem_per_warp_hp(int kh) { return kh * N_CODES * 128 + 2 * STREAM_RING + 2 * (MAX_RUN_HAPS + 2) * 8; }
 
 template <typename T>
 struct KernelParams {
@@ -86,6 +107,7 @@ struct KernelParams {
     const uint8_t *stream;               // one-hot coded haplotype columns + separators
     const int32_t *hap_len;              // per haplotype, stream order
     const Task *tasks;
+    const HTask *htasks;                 // haplotype-pair kernels
     const int32_t *ntasks_ptr;           // task count lives on the device (rescue lists)
     int32_t *counter;                    // dynamic task queue head
     const T *ph2pr;                      // [128]

@@ -145,12 +145,12 @@ def partition_lpt(cost, parts: int) -> np.ndarray:
     return owner
 
 
-def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True):
+def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True, fast=False):
     lib = load_library()
     keep = _Keep(fb)
     info = np.zeros(8 + 64, np.int64)
     cov = np.zeros(max(1, fb.n_pairs), np.uint8) if cover else None
-    rc = lib.phmm_plan_summary(C.byref(keep.c), C.c_int(precision), C.c_int(seg_cols),
+    rc = lib.phmm_plan_summary(C.byref(keep.c), C.c_int(precision | (0x100 if fast else 0)), C.c_int(seg_cols),
                                _ptr(info), _ptr(cov) if cover else None)
     if rc:
         raise PhmmError(rc, "phmm_plan_summary")

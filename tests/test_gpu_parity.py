@@ -143,6 +143,21 @@ def test_every_kernel_class_is_bit_exact():
                 check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, not fast, True)
 
 
+def test_every_haplotype_pair_class():
+    # the fast FP32 kernels: one read per lane group against two runs of haplotypes; batches with
+    # one haplotype leave the second run idle, odd read counts leave lane groups idle
+    for lanes in (32, 16, 8):
+        for kh in range(1, 17):
+            cap = kh * lanes - 1
+            fb = synth.generic(2000 + kh * 100 + lanes, 4, (3, 9), (1, 7), (max(1, cap - 40), cap), (10, 300),
+                               q_rng=(6, 45), subst=0.05, foreign_frac=0.2)
+            ref = oracle.run_port(fb)
+            for seg in (0, 512):
+                res, st = run(fb, force_class=(kh, lanes), fast=True, seg_cols=seg)
+                assert st["n_classes"] == 1
+                check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, False, True)
+
+
 def test_long_reads_multi_pass():
     # reads far beyond the largest register tile; haplotypes shorter and longer than the reads
     fb = synth.generic(51, 3, (3, 6), (2, 5), (256, 1500), (50, 2500), q_rng=(6, 45), subst=0.05, foreign_frac=0.3)

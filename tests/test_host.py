@@ -70,6 +70,18 @@ def test_plan_covers_every_pair_exactly_once(precision):
     assert (s["cover"] == 1).all()
 
 
+def test_fast_plan_pairs_runs_of_haplotypes():
+    # PHMM_OPT_FP32_KERNEL 1: haplotype-pair tasks (one read x two runs of haplotypes)
+    for fb in (synth.edge_cases(), synth.c1_small(0.03), synth.c2_large(60000), synth.c4_stress(800),
+               synth.c5_skewed(6000)):
+        for seg in (0, 300, 700):
+            s = phmm.plan_summary(fb, fast=True, seg_cols=seg)
+            assert s["pairs"] == fb.n_pairs and s["cells"] == fb.n_cells
+            assert (s["cover"] == 1).all()
+            for kh, lanes, vl, ntasks in s["classes"]:
+                assert lanes in (8, 16, 32) and 1 <= kh <= 16 and vl == 2 and ntasks > 0
+
+
 def test_plan_rejects_bad_input():
     with pytest.raises(phmm.PhmmError) as e:
         phmm.plan_summary(from_lists([([(b"", b"", b"", b"", b"")], [b"ACGT"])]))
