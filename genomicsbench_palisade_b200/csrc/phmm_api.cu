@@ -18,18 +18,62 @@ using namespace phmm;
 
 namespace {
 thread_local std::string g_create_error;
-}
+
+// Streams and events one workload in flight needs.  Class kernels of one phase run on the side
+// streams so that the tail of one persistent kernel (SMs idling while its last tasks finish) is
+// filled by the blocks of the next.
+struct StreamSet {
+    static const int N_SIDE = 4;
+    cudaStream_t main = nullptr;
+    cudaStream_t side[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};     // timing: start, FP32 done, FP64 done
+    cudaEvent_t ev_uploaded = nullptr;                     // inputs are in HBM (recorded on the upload stream)
+
+    cudaError_t create()
+    {
+        cudaError_t e;
+        if ((e = cudaStreamCreateWithFlags(&main, cudaStreamNonBlocking)) != cudaSuccess) return e;
+        for (int k = 0; k < 3; ++k)
+            if ((e = cudaEventCreate(&ev[k])) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&ev_uploaded, cudaEventDisableTiming)) != cudaSuccess) return e;
+        for (int k = 0; k < N_SIDE; ++k) {
+            if ((e = cudaStreamCreateWithFlags(&side[k], cudaStreamNonBlocking)) != cudaSuccess) return e;
+            if ((e = cudaEventCreateWithFlags(&ev_join[k], cudaEventDisableTiming)) != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    }
+    void destroy()
+    {
+        for (int k = 0; k < 3; ++k) if (ev[k]) cudaEventDestroy(ev[k]);
+        if (ev_fork) cudaEventDestroy(ev_fork);
+        if (ev_uploaded) cudaEventDestroy(ev_uploaded);
+        for (int k = 0; k < N_SIDE; ++k) {
+            if (ev_join[k]) cudaEventDestroy(ev_join[k]);
+            if (side[k]) cudaStreamDestroy(side[k]);
+        }
+        if (main) cudaStreamDestroy(main);
+    }
+};
+
+// Grow-only device arena: the host-buffer entry points carve a chunk's buffers out of it instead
+// of paying cudaMalloc / cudaFree (which synchronise the device) for every call.
+struct Arena {
+    uint8_t *base = nullptr;
+    size_t cap = 0, off = 0;
+};
+}  // namespace
 
 struct phmm_ctx {
     int device = 0;
     int sm_count = 0;
-    cudaStream_t stream = nullptr;
-    // class kernels of one phase run on side streams so that the tail of one persistent kernel
-    // (SMs idling while its last tasks finish) is filled by the blocks of the next
-    static const int N_SIDE = 4;
-    cudaStream_t side[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
-    cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    // slot 0 also serves the device-resident workload API; the host-buffer entry points pipeline
+    // chunks of batches through both slots (plan + upload of one chunk under the kernels of the other)
+    static const int N_SLOTS = 2;
+    StreamSet ss[N_SLOTS];
+    Arena arena[N_SLOTS];
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
     // device tables
     float *d_ph2pr_f = nullptr, *d_mm_f = nullptr;
     double *d_ph2pr_d = nullptr, *d_mm_d = nullptr;
@@ -38,13 +82,14 @@ struct phmm_ctx {
     int precision = 0, fp32_fast = 0, fp64_fast = 0, seg_cols = 0;
     int force_kh = 0, force_lanes = 0;
     int no_hp = 0;     // PHMM_NO_HP=1: fast FP32 kernels in the two-reads packing (A/B measurements)
+    int64_t chunk_cells = 0;   // host-buffer entry points: cells per pipelined chunk (0 = default)
     std::string error;
     std::mutex mu;     // the legacy symbols may be entered from several OpenMP threads
 };
 
 struct ClassDev {
     KClass kc;
-    int64_t task_off = 0;     // into d_tasks
+    int64_t task_off = 0;     // into d_tasks / d_htasks
     int32_t ntasks = 0;
 };
 
@@ -57,6 +102,8 @@ struct phmm_workload {
     int32_t resc_off[MAX_KH_SCALAR + 1];
     int32_t resc_cap[MAX_KH_SCALAR + 1];
     int precision = 0;
+    int planned_hp = 0;               // the plan holds haplotype-pair tasks: needs the fast FP32 kernels
+    Arena *arena = nullptr;           // non-NULL: buffers live in a context arena, nothing to free
     // device buffers
     uint8_t *d_pool = nullptr;        // 5 read pools back to back
     int64_t pool_stride = 0;
@@ -65,7 +112,6 @@ struct phmm_workload {
     ReadRec *d_reads = nullptr;
     Task *d_tasks = nullptr;
     HTask *d_htasks = nullptr;
-    int planned_hp = 0;               // the plan holds haplotype-pair tasks: needs the fast FP32 kernels
     Task *d_resc = nullptr, *d_guard = nullptr;
     int32_t *d_ints = nullptr;        // [0..63] queue heads, [64..] ntasks per class, resc/guard counts
     double *d_out = nullptr, *d_raw64 = nullptr;
@@ -74,6 +120,7 @@ struct phmm_workload {
     double *d_scratch = nullptr;      // multi-pass kernels: boundary rows, one slot per resident warp
     int64_t scratch_stride = 0;       // doubles per warp
     int scratch_blocks = 0;           // grid cap of the multi-pass kernels
+    int launches = 0;                 // kernels of the last launch
     int64_t last_rescued = 0, last_rescued_cells = 0, last_guard = 0;
 };
 
@@ -95,17 +142,11 @@ const int INTS_TOTAL = 192;
         }                                                                                     \
     } while (0)
 
-template <typename T>
-int dev_alloc(phmm_ctx *ctx, T **p, size_t n)
+double wall_ms()
 {
-    *p = nullptr;
-    if (n == 0) n = 1;
-    cudaError_t e = cudaMalloc((void **)p, n * sizeof(T));
-    if (e != cudaSuccess) {
-        ctx->error = std::string("cudaMalloc: ") + cudaGetErrorString(e);
-        return e == cudaErrorMemoryAllocation ? PHMM_ERR_NOMEM : PHMM_ERR_CUDA;
-    }
-    return PHMM_OK;
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
 }
 
 }  // namespace
@@ -175,20 +216,17 @@ extern "C" int phmm_create(int device, phmm_ctx **out)
     ctx->sm_count = prop.multiProcessorCount;
     if (const char *s = getenv("PHMM_FORCE_CLASS")) sscanf(s, "%d,%d", &ctx->force_kh, &ctx->force_lanes);
     if (const char *s = getenv("PHMM_NO_HP")) ctx->no_hp = atoi(s);
+    if (const char *s = getenv("PHMM_CHUNK_CELLS")) ctx->chunk_cells = atoll(s);
     auto bail = [&](const char *what, cudaError_t err) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
         phmm_destroy(ctx);
         return PHMM_ERR_CUDA;
     };
     if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
-    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
-    for (int k = 0; k < 4; ++k)
-        if ((e = cudaEventCreate(&ctx->ev[k])) != cudaSuccess) return bail("cudaEventCreate", e);
-    if ((e = cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-    for (int k = 0; k < phmm_ctx::N_SIDE; ++k) {
-        if ((e = cudaStreamCreateWithFlags(&ctx->side[k], cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
-        if ((e = cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-    }
+    for (int k = 0; k < phmm_ctx::N_SLOTS; ++k)
+        if ((e = ctx->ss[k].create()) != cudaSuccess) return bail("stream / event creation", e);
+    if ((e = cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     const HostTables &t = host_tables();
     if ((e = cudaMalloc(&ctx->d_ph2pr_f, 128 * sizeof(float))) != cudaSuccess) return bail("cudaMalloc", e);
     if ((e = cudaMalloc(&ctx->d_ph2pr_d, 128 * sizeof(double))) != cudaSuccess) return bail("cudaMalloc", e);
@@ -209,13 +247,12 @@ extern "C" int phmm_destroy(phmm_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaFree(ctx->d_ph2pr_f); cudaFree(ctx->d_ph2pr_d); cudaFree(ctx->d_mm_f); cudaFree(ctx->d_mm_d);
     cudaFree(ctx->d_bench);
-    for (int k = 0; k < 4; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
-    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
-    for (int k = 0; k < phmm_ctx::N_SIDE; ++k) {
-        if (ctx->ev_join[k]) cudaEventDestroy(ctx->ev_join[k]);
-        if (ctx->side[k]) cudaStreamDestroy(ctx->side[k]);
+    for (int k = 0; k < phmm_ctx::N_SLOTS; ++k) {
+        cudaFree(ctx->arena[k].base);
+        ctx->ss[k].destroy();
     }
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
+    if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
     delete ctx;
     return PHMM_OK;
 }
@@ -229,6 +266,7 @@ extern "C" int phmm_set_option(phmm_ctx *ctx, int option, int64_t value)
     case PHMM_OPT_FP64_KERNEL: if (value < 0 || value > 1) break; ctx->fp64_fast = (int)value; return PHMM_OK;
     case PHMM_OPT_SEG_COLS:    if (value < 0 || value > (1 << 24)) break; ctx->seg_cols = (int)value; return PHMM_OK;
     case PHMM_OPT_FORCE_CLASS: ctx->force_kh = (int)(value >> 8); ctx->force_lanes = (int)(value & 255); return PHMM_OK;
+    case PHMM_OPT_CHUNK_CELLS: if (value < 0) break; ctx->chunk_cells = value; return PHMM_OK;
     default: break;
     }
     ctx->error = "phmm_set_option: unknown option or value out of range";
@@ -244,6 +282,7 @@ extern "C" int64_t phmm_get_option(const phmm_ctx *ctx, int option)
     case PHMM_OPT_FP64_KERNEL: return ctx->fp64_fast;
     case PHMM_OPT_SEG_COLS: return ctx->seg_cols;
     case PHMM_OPT_FORCE_CLASS: return ((int64_t)ctx->force_kh << 8) | ctx->force_lanes;
+    case PHMM_OPT_CHUNK_CELLS: return ctx->chunk_cells;
     default: return -1;
     }
 }
@@ -260,7 +299,6 @@ extern "C" int phmm_get_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, dou
     if (consts_d) { consts_d[0] = t.init_d; consts_d[1] = t.log10_init_d; }
     return MM_REACHABLE;
 }
-
 // ============================================================================================
 // device-resident workloads
 // ============================================================================================
@@ -279,22 +317,24 @@ static PlanOptions plan_options(const phmm_ctx *ctx)
 extern "C" int phmm_workload_destroy(phmm_workload *w)
 {
     if (!w) return PHMM_OK;
-    if (w->ctx) cudaSetDevice(w->ctx->device);
-    cudaFree(w->d_pool); cudaFree(w->d_stream); cudaFree(w->d_hap_len); cudaFree(w->d_reads);
-    cudaFree(w->d_tasks); cudaFree(w->d_htasks); cudaFree(w->d_resc); cudaFree(w->d_guard); cudaFree(w->d_ints);
-    cudaFree(w->d_out); cudaFree(w->d_raw64); cudaFree(w->d_raw32); cudaFree(w->d_rescued);
-    cudaFree(w->d_scratch);
+    if (w->ctx && !w->arena) {
+        cudaSetDevice(w->ctx->device);
+        cudaFree(w->d_pool);          // one allocation holds every buffer of the workload
+    }
     delete w;
     return PHMM_OK;
 }
 
-extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, phmm_workload **out)
+// Plans `fb`, places the workload's buffers (in `arena` when given, which must be idle; else in one
+// cudaMalloc) and queues the uploads on `up`.  Does not wait for them: the caller orders later work
+// behind an event on `up`, or synchronises.
+static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, cudaStream_t up, phmm_workload **out)
 {
-    if (!ctx || !fb || !out) return PHMM_ERR_ARG;
     *out = nullptr;
     phmm_workload *w = new phmm_workload();
     w->ctx = ctx;
     w->precision = ctx->precision;
+    w->arena = arena;
     std::string err;
     int rc = build_plan(*fb, plan_options(ctx), &w->plan, &err);
     if (rc != PHMM_OK) { ctx->error = err; delete w; return rc; }
@@ -329,64 +369,99 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
         if (cp.kc.hp) w->planned_hp = 1;
         w->classes.push_back(cd);
     }
-#define WL_ALLOC(ptr, n)                                             \
-    do { int rc__ = dev_alloc(ctx, &(ptr), (size_t)(n)); if (rc__ != PHMM_OK) return fail(rc__); } while (0)
-    WL_ALLOC(w->d_pool, 5 * w->pool_stride);
-    WL_ALLOC(w->d_stream, P.stream.size());
-    WL_ALLOC(w->d_hap_len, P.hap_len.size());
-    WL_ALLOC(w->d_reads, P.reads.size());
-    WL_ALLOC(w->d_tasks, ntasks);
-    WL_ALLOC(w->d_htasks, nhtasks);
-    WL_ALLOC(w->d_ints, INTS_TOTAL);
-    WL_ALLOC(w->d_out, P.n_pairs);
-    WL_ALLOC(w->d_raw32, P.n_pairs);
-    WL_ALLOC(w->d_raw64, P.n_pairs);
-    WL_ALLOC(w->d_rescued, P.n_pairs);
-    if (need_resc) {
-        WL_ALLOC(w->d_resc, tot);
-        WL_ALLOC(w->d_guard, tot);
-    }
-    if (P.long_max_cols > 0 || P.resc_cap[0] > 0) {     // resc_cap[0]: reads whose rescue / guard class is the multi-pass kernel
-        // long reads may also come back as single-haplotype rescue / guard tasks
+    if (P.long_max_cols > 0 || P.resc_cap[0] > 0) {
+        // resc_cap[0]: reads whose rescue / guard class is the multi-pass kernel; long reads may
+        // also come back as single-haplotype rescue / guard tasks
         const int64_t cols = std::max<int64_t>(P.long_max_cols, P.max_haplen + SEP_COLS) + 64;
         w->scratch_stride = 6 * cols;
         w->scratch_blocks = ctx->sm_count * 2;
-        WL_ALLOC(w->d_scratch, w->scratch_stride * w->scratch_blocks * WARPS_PER_BLOCK);
     }
-#undef WL_ALLOC
+
+    // ---- one allocation, carved into 256-byte aligned pieces ------------------------------------
+    const size_t np = (size_t)std::max<int64_t>(1, P.n_pairs);
+    struct Piece { void **ptr; size_t bytes; };
+    const Piece pieces[] = {
+        {(void **)&w->d_pool, (size_t)(5 * w->pool_stride)},
+        {(void **)&w->d_stream, P.stream.size()},
+        {(void **)&w->d_hap_len, P.hap_len.size() * sizeof(int32_t)},
+        {(void **)&w->d_reads, P.reads.size() * sizeof(ReadRec)},
+        {(void **)&w->d_tasks, (size_t)ntasks * sizeof(Task)},
+        {(void **)&w->d_htasks, (size_t)nhtasks * sizeof(HTask)},
+        {(void **)&w->d_ints, INTS_TOTAL * sizeof(int32_t)},
+        {(void **)&w->d_out, np * sizeof(double)},
+        {(void **)&w->d_raw64, np * sizeof(double)},
+        {(void **)&w->d_raw32, np * sizeof(float)},
+        {(void **)&w->d_rescued, np},
+        {(void **)&w->d_resc, need_resc ? (size_t)tot * sizeof(Task) : 0},
+        {(void **)&w->d_guard, need_resc ? (size_t)tot * sizeof(Task) : 0},
+        {(void **)&w->d_scratch, (size_t)(w->scratch_stride * w->scratch_blocks * WARPS_PER_BLOCK) * sizeof(double)},
+    };
+    size_t total = 0;
+    for (const Piece &p : pieces) total += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255;
+    uint8_t *base = nullptr;
+    if (arena) {
+        if (arena->cap < total) {
+            cudaFree(arena->base);
+            arena->base = nullptr;
+            arena->cap = 0;
+            const size_t want = total + total / 4;
+            cudaError_t e = cudaMalloc((void **)&arena->base, want);
+            if (e != cudaSuccess) {
+                ctx->error = std::string("cudaMalloc (arena): ") + cudaGetErrorString(e);
+                return fail(e == cudaErrorMemoryAllocation ? PHMM_ERR_NOMEM : PHMM_ERR_CUDA);
+            }
+            arena->cap = want;
+        }
+        base = arena->base;
+    } else {
+        cudaError_t e = cudaMalloc((void **)&base, total);
+        if (e != cudaSuccess) {
+            ctx->error = std::string("cudaMalloc: ") + cudaGetErrorString(e);
+            return fail(e == cudaErrorMemoryAllocation ? PHMM_ERR_NOMEM : PHMM_ERR_CUDA);
+        }
+    }
+    {
+        size_t off = 0;
+        for (const Piece &p : pieces) {
+            *p.ptr = base + off;
+            off += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255;
+        }
+    }
+
 #define WL_TRY(expr)                                                                          \
     do {                                                                                      \
         cudaError_t e__ = (expr);                                                             \
         if (e__ != cudaSuccess) { ctx->error = std::string(#expr) + ": " + cudaGetErrorString(e__); return fail(PHMM_ERR_CUDA); } \
     } while (0)
-    cudaStream_t st = ctx->stream;
     const uint8_t *pools[5] = {fb->rs, fb->q, fb->i, fb->d, fb->c};
     int64_t h2d = 0;
     if (pool_len > 0)
         for (int k = 0; k < 5; ++k) {
-            WL_TRY(cudaMemcpyAsync(w->d_pool + k * w->pool_stride, pools[k] + P.pool_lo, (size_t)pool_len, cudaMemcpyHostToDevice, st));
+            WL_TRY(cudaMemcpyAsync(w->d_pool + k * w->pool_stride, pools[k] + P.pool_lo, (size_t)pool_len, cudaMemcpyHostToDevice, up));
             h2d += pool_len;
         }
-    WL_TRY(cudaMemcpyAsync(w->d_stream, P.stream.data(), P.stream.size(), cudaMemcpyHostToDevice, st));
-    WL_TRY(cudaMemcpyAsync(w->d_hap_len, P.hap_len.data(), P.hap_len.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    WL_TRY(cudaMemcpyAsync(w->d_stream, P.stream.data(), P.stream.size(), cudaMemcpyHostToDevice, up));
+    WL_TRY(cudaMemcpyAsync(w->d_hap_len, P.hap_len.data(), P.hap_len.size() * sizeof(int32_t), cudaMemcpyHostToDevice, up));
     if (!P.reads.empty())
-        WL_TRY(cudaMemcpyAsync(w->d_reads, P.reads.data(), P.reads.size() * sizeof(ReadRec), cudaMemcpyHostToDevice, st));
+        WL_TRY(cudaMemcpyAsync(w->d_reads, P.reads.data(), P.reads.size() * sizeof(ReadRec), cudaMemcpyHostToDevice, up));
     h2d += (int64_t)P.stream.size() + (int64_t)P.hap_len.size() * 4 + (int64_t)P.reads.size() * sizeof(ReadRec);
-    std::vector<int32_t> ints(INTS_TOTAL, 0);
+    int32_t ints[INTS_TOTAL];
+    memset(ints, 0, sizeof ints);
     for (size_t c = 0; c < P.classes.size(); ++c) {
         if (!P.classes[c].tasks.empty())
             WL_TRY(cudaMemcpyAsync(w->d_tasks + w->classes[c].task_off, P.classes[c].tasks.data(),
-                                   P.classes[c].tasks.size() * sizeof(Task), cudaMemcpyHostToDevice, st));
+                                   P.classes[c].tasks.size() * sizeof(Task), cudaMemcpyHostToDevice, up));
         if (!P.classes[c].htasks.empty())
             WL_TRY(cudaMemcpyAsync(w->d_htasks + w->classes[c].task_off, P.classes[c].htasks.data(),
-                                   P.classes[c].htasks.size() * sizeof(HTask), cudaMemcpyHostToDevice, st));
+                                   P.classes[c].htasks.size() * sizeof(HTask), cudaMemcpyHostToDevice, up));
         h2d += (int64_t)P.classes[c].tasks.size() * sizeof(Task) + (int64_t)P.classes[c].htasks.size() * sizeof(HTask);
         ints[INTS_NTASKS + c] = w->classes[c].ntasks;
     }
-    WL_TRY(cudaMemcpyAsync(w->d_ints, ints.data(), INTS_TOTAL * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-    WL_TRY(cudaMemsetAsync(w->d_raw64, 0, (size_t)std::max<int64_t>(1, P.n_pairs) * sizeof(double), st));
-    WL_TRY(cudaMemsetAsync(w->d_rescued, 0, (size_t)std::max<int64_t>(1, P.n_pairs), st));
-    WL_TRY(cudaStreamSynchronize(st));
+    // (copies from pageable host memory return once the source has been staged, so the plan's
+    // vectors and `ints` may be released right after)
+    WL_TRY(cudaMemcpyAsync(w->d_ints, ints, sizeof ints, cudaMemcpyHostToDevice, up));
+    WL_TRY(cudaMemsetAsync(w->d_raw64, 0, np * sizeof(double), up));
+    WL_TRY(cudaMemsetAsync(w->d_rescued, 0, np, up));
 #undef WL_TRY
     w->h2d_bytes = h2d;
     // host copies of the bulky plan parts are no longer needed
@@ -396,11 +471,27 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
     return PHMM_OK;
 }
 
-extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *stats)
+extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, phmm_workload **out)
 {
-    if (!ctx || !w || w->ctx != ctx) return PHMM_ERR_ARG;
+    if (!ctx || !fb || !out) return PHMM_ERR_ARG;
+    int rc = wl_create(ctx, fb, nullptr, ctx->ss[0].main, out);
+    if (rc != PHMM_OK) return rc;
+    if (cudaStreamSynchronize(ctx->ss[0].main) != cudaSuccess) {
+        ctx->error = "upload failed";
+        phmm_workload_destroy(*out);
+        *out = nullptr;
+        return PHMM_ERR_CUDA;
+    }
+    return PHMM_OK;
+}
+
+// Queues every kernel of the workload on the stream set `ss` (after `wait_for`, when given) and
+// records the timing events.  Does not wait.
+static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t wait_for)
+{
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
+    cudaStream_t st = ss.main;
+    if (wait_for) CUDA_TRY(ctx, cudaStreamWaitEvent(st, wait_for, 0));
     const HostTables &t = host_tables();
     const Plan &P = w->plan;
     const bool fast32 = ctx->fp32_fast != 0, fast64 = ctx->fp64_fast != 0;
@@ -464,22 +555,22 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
     int n_forked = 0;
     auto fork = [&]() -> cudaError_t {
         n_forked = 0;
-        return cudaEventRecord(ctx->ev_fork, st);
+        return cudaEventRecord(ss.ev_fork, st);
     };
     auto side_stream = [&](cudaStream_t *out) -> cudaError_t {
-        const int k = n_forked % phmm_ctx::N_SIDE;
-        if (n_forked < phmm_ctx::N_SIDE) {
-            cudaError_t e = cudaStreamWaitEvent(ctx->side[k], ctx->ev_fork, 0);
+        const int k = n_forked % StreamSet::N_SIDE;
+        if (n_forked < StreamSet::N_SIDE) {
+            cudaError_t e = cudaStreamWaitEvent(ss.side[k], ss.ev_fork, 0);
             if (e != cudaSuccess) return e;
         }
         ++n_forked;
-        *out = ctx->side[k];
+        *out = ss.side[k];
         return cudaSuccess;
     };
     auto join = [&]() -> cudaError_t {
-        for (int k = 0; k < std::min(n_forked, (int)phmm_ctx::N_SIDE); ++k) {
-            cudaError_t e = cudaEventRecord(ctx->ev_join[k], ctx->side[k]);
-            if (e == cudaSuccess) e = cudaStreamWaitEvent(st, ctx->ev_join[k], 0);
+        for (int k = 0; k < std::min(n_forked, (int)StreamSet::N_SIDE); ++k) {
+            cudaError_t e = cudaEventRecord(ss.ev_join[k], ss.side[k]);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(st, ss.ev_join[k], 0);
             if (e != cudaSuccess) return e;
         }
         n_forked = 0;
@@ -487,7 +578,7 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
     };
     cudaStream_t ks = st;
 
-    CUDA_TRY(ctx, cudaEventRecord(ctx->ev[0], st));
+    CUDA_TRY(ctx, cudaEventRecord(ss.ev[0], st));
     // ---- main pass over the planned tasks ---------------------------------------------------
     CUDA_TRY(ctx, fork());
     for (size_t c = 0; c < w->classes.size(); ++c) {
@@ -535,7 +626,7 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
         }
         CUDA_TRY(ctx, join());
     }
-    CUDA_TRY(ctx, cudaEventRecord(ctx->ev[1], st));
+    CUDA_TRY(ctx, cudaEventRecord(ss.ev[1], st));
     // ---- FP64 rescue (IntelPairHmmCSource.cpp:73-75) --------------------------------------------
     if (mode == 0) {
         CUDA_TRY(ctx, fork());
@@ -553,11 +644,17 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
         }
         CUDA_TRY(ctx, join());
     }
-    CUDA_TRY(ctx, cudaEventRecord(ctx->ev[2], st));
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, cudaEventRecord(ss.ev[2], st));
+    w->launches = launches;
+    return PHMM_OK;
+}
 
+// After the stream set has drained: list counters and event times of the last launch.
+static int wl_finish(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, phmm_stats *stats)
+{
     int32_t counts[32];
-    CUDA_TRY(ctx, cudaMemcpy(counts, w->d_ints + INTS_RESC, sizeof counts, cudaMemcpyDeviceToHost));
+    CUDA_TRY(ctx, cudaMemcpyAsync(counts, w->d_ints + INTS_RESC, sizeof counts, cudaMemcpyDeviceToHost, ss.main));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
     int64_t nres = 0, nguard = 0;
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nres += counts[k]; nguard += counts[16 + k]; }
     w->last_rescued = nres;
@@ -568,15 +665,24 @@ extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *st
         stats->n_cells = w->n_cells;
         stats->n_rescued = nres;
         stats->n_guard = nguard;
-        stats->n_launches = launches;
+        stats->n_launches = w->launches;
         stats->n_classes = (int32_t)w->classes.size();
         for (auto &cd : w->classes) stats->n_tasks += cd.ntasks;
         stats->h2d_bytes = w->h2d_bytes;
-        cudaEventElapsedTime(&stats->ms_fp32, ctx->ev[0], ctx->ev[1]);
-        cudaEventElapsedTime(&stats->ms_fp64, ctx->ev[1], ctx->ev[2]);
-        cudaEventElapsedTime(&stats->ms_total, ctx->ev[0], ctx->ev[2]);
+        cudaEventElapsedTime(&stats->ms_fp32, ss.ev[0], ss.ev[1]);
+        cudaEventElapsedTime(&stats->ms_fp64, ss.ev[1], ss.ev[2]);
+        cudaEventElapsedTime(&stats->ms_total, ss.ev[0], ss.ev[2]);
     }
     return PHMM_OK;
+}
+
+extern "C" int phmm_workload_run(phmm_ctx *ctx, phmm_workload *w, phmm_stats *stats)
+{
+    if (!ctx || !w || w->ctx != ctx) return PHMM_ERR_ARG;
+    int rc = wl_launch(ctx, w, ctx->ss[0], nullptr);
+    if (rc != PHMM_OK) return rc;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->ss[0].main));
+    return wl_finish(ctx, w, ctx->ss[0], stats);
 }
 
 extern "C" int phmm_workload_results(phmm_ctx *ctx, phmm_workload *w, double *out, float *raw32, double *raw64,
@@ -586,46 +692,139 @@ extern "C" int phmm_workload_results(phmm_ctx *ctx, phmm_workload *w, double *ou
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const size_t n = (size_t)w->n_pairs;
     if (n == 0) return PHMM_OK;
-    if (out) CUDA_TRY(ctx, cudaMemcpyAsync(out, w->d_out, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-    if (raw32) CUDA_TRY(ctx, cudaMemcpyAsync(raw32, w->d_raw32, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
-    if (raw64) CUDA_TRY(ctx, cudaMemcpyAsync(raw64, w->d_raw64, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-    if (rescued) CUDA_TRY(ctx, cudaMemcpyAsync(rescued, w->d_rescued, n, cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaStream_t st = ctx->ss[0].main;
+    if (out) CUDA_TRY(ctx, cudaMemcpyAsync(out, w->d_out, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (raw32) CUDA_TRY(ctx, cudaMemcpyAsync(raw32, w->d_raw32, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (raw64) CUDA_TRY(ctx, cudaMemcpyAsync(raw64, w->d_raw64, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (rescued) CUDA_TRY(ctx, cudaMemcpyAsync(rescued, w->d_rescued, n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
     return PHMM_OK;
 }
 
 // ============================================================================================
 // host-buffer entry points
 // ============================================================================================
-static double wall_ms()
-{
-    struct timespec ts;
-    clock_gettime(CLOCK_MONOTONIC, &ts);
-    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
-}
-
+// The batches are cut into chunks of about `chunk_cells` cells.  Chunk c is planned and uploaded
+// by the host while the kernels of chunk c - 1 run (its buffers live in the other arena, its
+// kernels queue on the other stream set, so they also fill the tail of chunk c - 1), and the
+// results of chunk c - 1 are copied back while chunk c runs.  Exposed to the caller are only the
+// plan + upload of the first chunk and the copy-back of the last.
 extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, double *out, phmm_stats *stats)
 {
     if (!ctx || !fb) return PHMM_ERR_ARG;
-    phmm_workload *w = nullptr;
-    const double t0 = wall_ms();
-    int rc = phmm_workload_create(ctx, fb, &w);
-    if (rc != PHMM_OK) return rc;
-    const double t1 = wall_ms();
-    phmm_stats s;
-    rc = phmm_workload_run(ctx, w, &s);
-    if (rc == PHMM_OK && w->n_pairs > 0 && !out) { ctx->error = "NULL output"; rc = PHMM_ERR_ARG; }
-    const double t2 = wall_ms();
-    if (rc == PHMM_OK) rc = phmm_workload_results(ctx, w, out, nullptr, nullptr, nullptr);
-    const double t3 = wall_ms();
-    if (stats && rc == PHMM_OK) {
-        *stats = s;
-        stats->ms_h2d = (float)(t1 - t0);      // plan + upload
-        stats->ms_d2h = (float)(t3 - t2);
-        stats->d2h_bytes = w->n_pairs * (int64_t)sizeof(double);
+    if (fb->n_batches < 0 || (fb->n_batches && (!fb->batch_num_reads || !fb->batch_num_haps))) {
+        ctx->error = "malformed batch table";
+        return PHMM_ERR_ARG;
     }
-    phmm_workload_destroy(w);
-    return rc;
+    if ((fb->n_reads > 0 && !fb->read_len) || (fb->n_haps > 0 && !fb->hap_len) || fb->n_reads < 0 || fb->n_haps < 0) {
+        ctx->error = "NULL read / haplotype table";
+        return PHMM_ERR_ARG;
+    }
+    const double t_begin = wall_ms();
+    // ---- chunk boundaries (whole batches), by cells --------------------------------------------
+    struct Chunk { int64_t b0, b1, r0, r1, h0, h1, p0, p1; };
+    std::vector<Chunk> chunks;
+    {
+        std::vector<int64_t> cells((size_t)fb->n_batches, 0);
+        int64_t r = 0, h = 0, total = 0;
+        for (int64_t b = 0; b < fb->n_batches; ++b) {
+            const int nr = fb->batch_num_reads[b], nh = fb->batch_num_haps[b];
+            if (nr < 0 || nh < 0 || r + nr > fb->n_reads || h + nh > fb->n_haps) {
+                ctx->error = "batch tables do not add up to n_reads / n_haps";
+                return PHMM_ERR_ARG;
+            }
+            int64_t sr = 0, sh = 0;
+            for (int k = 0; k < nr; ++k) sr += fb->read_len[r + k];
+            for (int k = 0; k < nh; ++k) sh += fb->hap_len[h + k];
+            cells[b] = sr * sh;
+            total += cells[b];
+            r += nr; h += nh;
+        }
+        // default: chunks of >= 1.2e10 cells (a few ms of kernels), at most 12; the first one half
+        // that size so the device starts early
+        int64_t per = ctx->chunk_cells > 0 ? ctx->chunk_cells : std::max<int64_t>(12000000000ll, total / 12 + 1);
+        Chunk c{0, 0, 0, 0, 0, 0, 0, 0};
+        int64_t acc = 0;
+        r = 0; h = 0;
+        int64_t p = 0;
+        for (int64_t b = 0; b < fb->n_batches; ++b) {
+            const int nr = fb->batch_num_reads[b], nh = fb->batch_num_haps[b];
+            acc += cells[b];
+            r += nr; h += nh; p += (int64_t)nr * nh;
+            const int64_t want = chunks.empty() ? per / 2 : per;
+            if (acc >= want || b == fb->n_batches - 1) {
+                c.b1 = b + 1; c.r1 = r; c.h1 = h; c.p1 = p;
+                chunks.push_back(c);
+                c = Chunk{b + 1, b + 1, r, r, h, h, p, p};
+                acc = 0;
+            }
+        }
+        if (chunks.empty()) chunks.push_back(Chunk{0, 0, 0, 0, 0, 0, 0, 0});
+    }
+    if (chunks.back().p1 > 0 && !out) { ctx->error = "NULL output"; return PHMM_ERR_ARG; }
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+
+    phmm_workload *wl[phmm_ctx::N_SLOTS] = {nullptr, nullptr};
+    phmm_stats agg;
+    memset(&agg, 0, sizeof agg);
+    int rc = PHMM_OK;
+    double t_first_launch = 0, ms_d2h = 0;
+    // copy chunk j's results back (waits for its kernels), collect its statistics, release it
+    auto retire = [&](size_t j) -> int {
+        const int slot = (int)(j % phmm_ctx::N_SLOTS);
+        phmm_workload *w = wl[slot];
+        StreamSet &ss = ctx->ss[slot];
+        const double t0 = wall_ms();
+        if (w->n_pairs > 0) {
+            // pageable destination: the call returns when the copy is complete
+            CUDA_TRY(ctx, cudaMemcpyAsync(out + chunks[j].p0, w->d_out, (size_t)w->n_pairs * sizeof(double),
+                                          cudaMemcpyDeviceToHost, ss.main));
+        }
+        phmm_stats s;
+        int r2 = wl_finish(ctx, w, ss, &s);
+        ms_d2h += wall_ms() - t0;
+        if (r2 != PHMM_OK) return r2;
+        agg.n_pairs += s.n_pairs; agg.n_cells += s.n_cells; agg.n_rescued += s.n_rescued;
+        agg.n_guard += s.n_guard; agg.n_tasks += s.n_tasks; agg.h2d_bytes += s.h2d_bytes;
+        agg.n_launches += s.n_launches; agg.n_classes = std::max(agg.n_classes, s.n_classes);
+        agg.ms_fp32 += s.ms_fp32; agg.ms_fp64 += s.ms_fp64; agg.ms_total += s.ms_total;
+        agg.d2h_bytes += w->n_pairs * (int64_t)sizeof(double);
+        phmm_workload_destroy(w);
+        wl[slot] = nullptr;
+        return PHMM_OK;
+    };
+    for (size_t j = 0; j < chunks.size() && rc == PHMM_OK; ++j) {
+        const int slot = (int)(j % phmm_ctx::N_SLOTS);
+        if (wl[slot]) rc = retire(j - phmm_ctx::N_SLOTS);      // the slot's arena must be idle
+        if (rc != PHMM_OK) break;
+        const Chunk &c = chunks[j];
+        phmm_flat_batches sub = *fb;
+        sub.n_batches = c.b1 - c.b0; sub.n_reads = c.r1 - c.r0; sub.n_haps = c.h1 - c.h0;
+        sub.batch_num_reads = fb->batch_num_reads + c.b0; sub.batch_num_haps = fb->batch_num_haps + c.b0;
+        sub.read_len = fb->read_len + c.r0; sub.read_off = fb->read_off + c.r0;
+        sub.hap_len = fb->hap_len + c.h0; sub.hap_off = fb->hap_off + c.h0;
+        StreamSet &ss = ctx->ss[slot];
+        rc = wl_create(ctx, &sub, &ctx->arena[slot], ctx->copy_in, &wl[slot]);
+        if (rc != PHMM_OK) break;
+        if (cudaEventRecord(ss.ev_uploaded, ctx->copy_in) != cudaSuccess) { ctx->error = "cudaEventRecord failed"; rc = PHMM_ERR_CUDA; break; }
+        rc = wl_launch(ctx, wl[slot], ss, ss.ev_uploaded);
+        if (j == 0) t_first_launch = wall_ms();
+        // with the next chunk queued, wait for the previous one and fetch its results
+        if (rc == PHMM_OK && j >= 1 && wl[(j - 1) % phmm_ctx::N_SLOTS]) rc = retire(j - 1);
+    }
+    for (size_t j = chunks.size() >= 2 ? chunks.size() - 2 : 0; j < chunks.size() && rc == PHMM_OK; ++j)
+        if (wl[j % phmm_ctx::N_SLOTS]) rc = retire(j);
+    if (rc != PHMM_OK) {
+        cudaDeviceSynchronize();
+        for (int k = 0; k < phmm_ctx::N_SLOTS; ++k) { phmm_workload_destroy(wl[k]); wl[k] = nullptr; }
+        return rc;
+    }
+    if (stats) {
+        *stats = agg;
+        stats->ms_h2d = (float)(t_first_launch - t_begin);   // exposed: plan + upload of the first chunk
+        stats->ms_d2h = (float)ms_d2h;                       // host time in result copies (mostly overlapped)
+    }
+    return PHMM_OK;
 }
 
 namespace {
@@ -783,15 +982,15 @@ extern "C" int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s,
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const int grid = ctx->sm_count * 8, iters = 4096;
     double ops_per_thread = 0;
-    CUDA_TRY(ctx, launch_pipe_bench(which, ctx->d_bench, grid, 64, ctx->stream, &ops_per_thread));   // warm-up
+    CUDA_TRY(ctx, launch_pipe_bench(which, ctx->d_bench, grid, 64, ctx->ss[0].main, &ops_per_thread));   // warm-up
     float best = 1e30f;
     for (int rep = 0; rep < 3; ++rep) {
-        CUDA_TRY(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
-        CUDA_TRY(ctx, launch_pipe_bench(which, ctx->d_bench, grid, iters, ctx->stream, &ops_per_thread));
-        CUDA_TRY(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ss[0].ev[0], ctx->ss[0].main));
+        CUDA_TRY(ctx, launch_pipe_bench(which, ctx->d_bench, grid, iters, ctx->ss[0].main, &ops_per_thread));
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ss[0].ev[1], ctx->ss[0].main));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->ss[0].main));
         float ms = 0;
-        CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+        CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ss[0].ev[0], ctx->ss[0].ev[1]));
         best = std::min(best, ms);
     }
     *lane_ops_per_s = ops_per_thread * 256.0 * grid / (best * 1e-3);

@@ -18,7 +18,7 @@ from .batches import FlatBatches
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libphmm_cuda.so")
 
-OPT_PRECISION, OPT_FP32_KERNEL, OPT_FP64_KERNEL, OPT_SEG_COLS, OPT_FORCE_CLASS = 1, 2, 3, 4, 6
+OPT_PRECISION, OPT_FP32_KERNEL, OPT_FP64_KERNEL, OPT_SEG_COLS, OPT_FORCE_CLASS, OPT_CHUNK_CELLS = 1, 2, 3, 4, 6, 7
 BOTH, FLOAT_ONLY, DOUBLE_ONLY = 0, 1, 2
 ERRORS = {1: "PHMM_ERR_ARG", 2: "PHMM_ERR_EMPTY_SEQ", 3: "PHMM_ERR_TOO_LONG", 4: "PHMM_ERR_CUDA",
           5: "PHMM_ERR_NOMEM", 6: "PHMM_ERR_PARSE", 7: "PHMM_ERR_IO"}
@@ -219,7 +219,7 @@ class PairHMM:
     """One context on one B200 (phmm_create = the reference's initPairHMM)."""
 
     def __init__(self, device: int = 0, precision: int = BOTH, fast: bool = False, fast64: bool = False,
-                 seg_cols: int = 0, force_class=None):
+                 seg_cols: int = 0, force_class=None, chunk_cells: int = 0):
         self.lib = load_library()
         self._h = C.c_void_p()
         rc = self.lib.phmm_create(C.c_int(device), C.byref(self._h))
@@ -231,6 +231,8 @@ class PairHMM:
         self.set_option(OPT_SEG_COLS, seg_cols)
         if force_class:
             self.set_option(OPT_FORCE_CLASS, (force_class[0] << 8) | force_class[1])
+        if chunk_cells:
+            self.set_option(OPT_CHUNK_CELLS, chunk_cells)
 
     def _check(self, rc):
         if rc:
@@ -242,10 +244,13 @@ class PairHMM:
     def workload(self, fb: FlatBatches) -> Workload:
         return Workload(self, fb)
 
-    def compute(self, fb: FlatBatches, stats=False):
-        """Host buffers in, log10 likelihoods out (phmm_compute_flat)."""
+    def compute(self, fb: FlatBatches, stats=False, out=None):
+        """Host buffers in, log10 likelihoods out (phmm_compute_flat).  `out`: caller-owned float64
+        array of fb.n_pairs to fill (as the reference driver reuses its results buffer)."""
         keep = _Keep(fb)
-        out = np.zeros(fb.n_pairs, np.float64)
+        if out is None:
+            out = np.zeros(fb.n_pairs, np.float64)
+        assert out.dtype == np.float64 and out.size >= fb.n_pairs and out.flags.c_contiguous
         st = CStats()
         self._check(self.lib.phmm_compute_flat(self._h, C.byref(keep.c), _ptr(out), C.byref(st)))
         return (out, st.as_dict()) if stats else out

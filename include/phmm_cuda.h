@@ -112,6 +112,9 @@ typedef struct {
 #define PHMM_OPT_FORCE_CLASS 6   /* benchmarking: pin the kernel class, value = kh << 8 | lanes
                                     (0 = choose per read length); also env PHMM_FORCE_CLASS=kh,lanes */
 
+#define PHMM_OPT_CHUNK_CELLS 7   /* host-buffer entry points: cells per pipelined chunk of batches
+                                    (0 = default: >= 1.2e10, at most 12 chunks); also env PHMM_CHUNK_CELLS */
+
 typedef struct phmm_ctx phmm_ctx;
 typedef struct phmm_workload phmm_workload;
 

@@ -118,6 +118,24 @@ def test_host_entry_points_agree():
     assert same_or_close(a, g["out"], RTOL_FP32)
 
 
+def test_host_entry_point_pipelines_chunks():
+    # phmm_compute_flat cuts the batches into chunks and overlaps plan + upload of one with the kernels
+    # of the other: any chunk size must give the results of the single device-resident workload
+    fb = synth.generic(77, 23, (5, 40), (1, 9), (20, 300), (30, 500), q_rng=(6, 45), subst=0.05, foreign_frac=0.2)
+    ref = oracle.run_port(fb)
+    for fast in (False, True):
+        res, _ = run(fb, fast=fast)
+        for chunk in (1, 200_000, 3_000_000, 0):
+            eng = phmm.PairHMM(fast=fast, chunk_cells=chunk)
+            out, st = eng.compute(fb, stats=True)
+            out2 = eng.compute(fb, out=np.empty(fb.n_pairs))        # arenas reused
+            eng.close()
+            assert np.array_equal(out, res[0]) and np.array_equal(out2, out)
+            assert st["n_pairs"] == fb.n_pairs and st["n_cells"] == fb.n_cells
+            assert st["n_rescued"] == int(ref.rescued.sum())
+    assert same_or_close(res[0][ref.rescued == 0], ref.out[ref.rescued == 0], RTOL_FP32)
+
+
 def test_random_workloads_against_the_oracle():
     for fb in (synth.generic(31, 12, (1, 60), (1, 20), (1, 255), (1, 700), q_rng=(6, 45), subst=0.08,
                              foreign_frac=0.15),
