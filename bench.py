@@ -82,7 +82,7 @@ def my_batches(fb, rank: int, world: int):
 
 def make_shard(name: str, rank: int, world: int):
     fb = make_workload(name, world)
-    return fb, fb.select_batches(my_batches(fb, rank, world))
+    return fb, (fb if world == 1 else fb.select_batches(my_batches(fb, rank, world), compact=True))
 
 
 # ---------------------------------------------------------------------------------------------
@@ -216,6 +216,7 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--kernel", default=os.environ.get("PHMM_BENCH_KERNEL", "fast"), choices=["exact", "fast"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -289,18 +290,18 @@ def main():
 
     # ---- end to end through the host-buffer C ABI (e2e) --------------------------------------------
     o = np.empty(fb.n_pairs, np.float64)          # the caller's results buffer, reused as the driver does
-    for _ in range(2):
+    for _ in range(0 if args.no_e2e else 2):
         eng.compute(fb, out=o)
     o.fill(0.0)
     barrier()
     te = time.perf_counter()
     h2d = d2h = 0
-    for _ in range(args.steps):
+    for _ in range(0 if args.no_e2e else args.steps):
         o, s2 = eng.compute(fb, stats=True, out=o)
         h2d, d2h = s2["h2d_bytes"], s2["d2h_bytes"]
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - te) * 1e3 / args.steps)
-    e2e_ok = bool(np.array_equal(o, out))
+    e2e_ok = bool(np.array_equal(o, out)) if not args.no_e2e else None
     h2d_all, d2h_all = sum_over_ranks(h2d), sum_over_ranks(d2h)
 
     if rank == 0:
@@ -322,10 +323,13 @@ def main():
             "gpu_launches": int(st["n_launches"]) * args.steps,
             "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                          "traffic": None,
-                         "kernel": "phmm_forward_kernel<float,...> (all FP32 classes of the step, rank 0)",
+                         "kernel": ("phmm_forward_hp_kernel<KH, LANES>" if fast else "phmm_forward_kernel<float, KH, LANES>")
+                                   + " (all FP32 class instantiations of the step together, rank 0)",
                          "how": "12 flop/cell x cells / CUDA-event time of the FP32 launches; peak = 2 x FFMA lane-ops/s "
                                 "measured by phmm_microbench on this device in this run (MEASURED_PEAKS.json has no FP32 entry)",
-                         "fma_pipe_slot_frac": ach / peak * 2 * ((8.0 if fast else 12.0) / 12.0),
+                         # FP32 lane-operations issued per cell / FFMA lane-ops peak: 6.25 packed instructions per
+                         # cell pair in the fast kernels (scaled recurrence, 16-row tiles), 12 unfused in the exact ones
+                         "fma_pipe_slot_frac": ach / peak * 2 * ((6.25 if fast else 12.0) / 12.0),
                          "ms_fp32": ms32 / args.steps, "ms_fp64": ms64 / args.steps},
             "rescue": {"pairs": int(resc.sum()), "frac": float(resc.mean()) if resc.size else 0.0, "cells": resc_cells,
                        "guard_band_pairs": int(st["n_guard"])},

@@ -110,17 +110,28 @@ class FlatBatches:
         return rsl.astype(np.int64) * hpl.astype(np.int64)
 
     # ---- slicing (multi-GPU sharding keeps whole batches) -------------------------------------
-    def select_batches(self, idx) -> "FlatBatches":
+    def select_batches(self, idx, compact=False) -> "FlatBatches":
         idx = np.asarray(idx, dtype=np.int64)
         brs, bhs = self.batch_read_start, self.batch_hap_start
         r_idx = (np.concatenate([np.arange(brs[b], brs[b + 1]) for b in idx])
                  if len(idx) else np.zeros(0, np.int64))
         h_idx = (np.concatenate([np.arange(bhs[b], bhs[b + 1]) for b in idx])
                  if len(idx) else np.zeros(0, np.int64))
-        return FlatBatches(self.batch_num_reads[idx], self.batch_num_haps[idx],
-                           self.read_len[r_idx], self.read_off[r_idx],
-                           self.rs, self.q, self.i, self.d, self.c,
-                           self.hap_len[h_idx], self.hap_off[h_idx], self.hap, dict(self.meta))
+        if not compact:
+            return FlatBatches(self.batch_num_reads[idx], self.batch_num_haps[idx],
+                               self.read_len[r_idx], self.read_off[r_idx],
+                               self.rs, self.q, self.i, self.d, self.c,
+                               self.hap_len[h_idx], self.hap_off[h_idx], self.hap, dict(self.meta))
+        # own pools holding only the selected reads / haplotypes (what a rank of a sharded run keeps)
+        def gather(lens, offs, pools):
+            lens = lens.astype(np.int64)
+            new_off = np.concatenate(([0], np.cumsum(lens)))[:-1] if len(lens) else np.zeros(0, np.int64)
+            src = (np.repeat(offs - new_off, lens) + np.arange(int(lens.sum()))) if len(lens) else np.zeros(0, np.int64)
+            return new_off, [np.ascontiguousarray(p[src]) for p in pools]
+        r_off, (rs, q, i, d, c) = gather(self.read_len[r_idx], self.read_off[r_idx], (self.rs, self.q, self.i, self.d, self.c))
+        h_off, (hap,) = gather(self.hap_len[h_idx], self.hap_off[h_idx], (self.hap,))
+        return FlatBatches(self.batch_num_reads[idx], self.batch_num_haps[idx], self.read_len[r_idx], r_off,
+                           rs, q, i, d, c, self.hap_len[h_idx], h_off, hap, dict(self.meta))
 
     def select_reads(self, keep):
         """Drop reads where `keep` is False.  Returns (batches, pair_index) with pair_index[k] the

@@ -121,6 +121,7 @@ struct phmm_workload {
     int64_t scratch_stride = 0;       // doubles per warp
     int scratch_blocks = 0;           // grid cap of the multi-pass kernels
     int launches = 0;                 // kernels of the last launch
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // timing of the last launch: start, FP32 done, FP64 done
     int64_t last_rescued = 0, last_rescued_cells = 0, last_guard = 0;
 };
 
@@ -299,6 +300,62 @@ extern "C" int phmm_get_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, dou
     if (consts_d) { consts_d[0] = t.init_d; consts_d[1] = t.log10_init_d; }
     return MM_REACHABLE;
 }
+namespace {
+// A range of whole batches of a phmm_flat_batches and the reads / haplotypes / pairs it spans.
+struct Chunk { int64_t b0, b1, r0, r1, h0, h1, p0, p1; };
+
+// Cuts the batches into consecutive chunks of about `per` cells (0: max(min_cells, total / max_chunks)).
+int split_batches(phmm_ctx *ctx, const phmm_flat_batches *fb, int64_t per, int64_t min_cells, int max_chunks,
+                  bool small_first, std::vector<Chunk> *out)
+{
+    std::vector<Chunk> &chunks = *out;
+    chunks.clear();
+    std::vector<int64_t> cells((size_t)fb->n_batches, 0);
+    int64_t r = 0, h = 0, total = 0;
+    for (int64_t b = 0; b < fb->n_batches; ++b) {
+        const int nr = fb->batch_num_reads[b], nh = fb->batch_num_haps[b];
+        if (nr < 0 || nh < 0 || r + nr > fb->n_reads || h + nh > fb->n_haps) {
+            ctx->error = "batch tables do not add up to n_reads / n_haps";
+            return PHMM_ERR_ARG;
+        }
+        int64_t sr = 0, sh = 0;
+        for (int k = 0; k < nr; ++k) sr += fb->read_len[r + k];
+        for (int k = 0; k < nh; ++k) sh += fb->hap_len[h + k];
+        cells[b] = sr * sh;
+        total += cells[b];
+        r += nr; h += nh;
+    }
+    if (per <= 0) per = std::max<int64_t>(min_cells, total / max_chunks + 1);
+    Chunk c{0, 0, 0, 0, 0, 0, 0, 0};
+    int64_t acc = 0, p = 0;
+    r = 0; h = 0;
+    for (int64_t b = 0; b < fb->n_batches; ++b) {
+        const int nr = fb->batch_num_reads[b], nh = fb->batch_num_haps[b];
+        acc += cells[b];
+        r += nr; h += nh; p += (int64_t)nr * nh;
+        const int64_t want = (small_first && chunks.empty()) ? per / 2 : per;
+        if (acc >= want || b == fb->n_batches - 1) {
+            c.b1 = b + 1; c.r1 = r; c.h1 = h; c.p1 = p;
+            chunks.push_back(c);
+            c = Chunk{b + 1, b + 1, r, r, h, h, p, p};
+            acc = 0;
+        }
+    }
+    if (chunks.empty()) chunks.push_back(Chunk{0, 0, 0, 0, 0, 0, 0, 0});
+    return PHMM_OK;
+}
+
+phmm_flat_batches sub_batches(const phmm_flat_batches *fb, const Chunk &c)
+{
+    phmm_flat_batches sub = *fb;
+    sub.n_batches = c.b1 - c.b0; sub.n_reads = c.r1 - c.r0; sub.n_haps = c.h1 - c.h0;
+    sub.batch_num_reads = fb->batch_num_reads + c.b0; sub.batch_num_haps = fb->batch_num_haps + c.b0;
+    sub.read_len = fb->read_len + c.r0; sub.read_off = fb->read_off + c.r0;
+    sub.hap_len = fb->hap_len + c.h0; sub.hap_off = fb->hap_off + c.h0;
+    return sub;
+}
+}  // namespace
+
 // ============================================================================================
 // device-resident workloads
 // ============================================================================================
@@ -317,6 +374,7 @@ static PlanOptions plan_options(const phmm_ctx *ctx)
 extern "C" int phmm_workload_destroy(phmm_workload *w)
 {
     if (!w) return PHMM_OK;
+    for (int k = 0; k < 3; ++k) if (w->ev[k]) cudaEventDestroy(w->ev[k]);
     if (w->ctx && !w->arena) {
         cudaSetDevice(w->ctx->device);
         cudaFree(w->d_pool);          // one allocation holds every buffer of the workload
@@ -345,6 +403,9 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
 
     auto fail = [&](int code) { phmm_workload_destroy(w); return code; };
     if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->error = "cudaSetDevice failed"; return fail(PHMM_ERR_CUDA); }
+
+    for (int k = 0; k < 3; ++k)
+        if (cudaEventCreate(&w->ev[k]) != cudaSuccess) { ctx->error = "cudaEventCreate failed"; return fail(PHMM_ERR_CUDA); }
 
     // rescue / guard lists: one per scalar class, sized for every pair of that class
     int64_t tot = 0;
@@ -578,7 +639,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     };
     cudaStream_t ks = st;
 
-    CUDA_TRY(ctx, cudaEventRecord(ss.ev[0], st));
+    CUDA_TRY(ctx, cudaEventRecord(w->ev[0], st));
     // ---- main pass over the planned tasks ---------------------------------------------------
     CUDA_TRY(ctx, fork());
     for (size_t c = 0; c < w->classes.size(); ++c) {
@@ -626,7 +687,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
         }
         CUDA_TRY(ctx, join());
     }
-    CUDA_TRY(ctx, cudaEventRecord(ss.ev[1], st));
+    CUDA_TRY(ctx, cudaEventRecord(w->ev[1], st));
     // ---- FP64 rescue (IntelPairHmmCSource.cpp:73-75) --------------------------------------------
     if (mode == 0) {
         CUDA_TRY(ctx, fork());
@@ -644,7 +705,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
         }
         CUDA_TRY(ctx, join());
     }
-    CUDA_TRY(ctx, cudaEventRecord(ss.ev[2], st));
+    CUDA_TRY(ctx, cudaEventRecord(w->ev[2], st));
     w->launches = launches;
     return PHMM_OK;
 }
@@ -669,9 +730,9 @@ static int wl_finish(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, phmm_stats 
         stats->n_classes = (int32_t)w->classes.size();
         for (auto &cd : w->classes) stats->n_tasks += cd.ntasks;
         stats->h2d_bytes = w->h2d_bytes;
-        cudaEventElapsedTime(&stats->ms_fp32, ss.ev[0], ss.ev[1]);
-        cudaEventElapsedTime(&stats->ms_fp64, ss.ev[1], ss.ev[2]);
-        cudaEventElapsedTime(&stats->ms_total, ss.ev[0], ss.ev[2]);
+        cudaEventElapsedTime(&stats->ms_fp32, w->ev[0], w->ev[1]);
+        cudaEventElapsedTime(&stats->ms_fp64, w->ev[1], w->ev[2]);
+        cudaEventElapsedTime(&stats->ms_total, w->ev[0], w->ev[2]);
     }
     return PHMM_OK;
 }
@@ -712,54 +773,13 @@ extern "C" int phmm_workload_results(phmm_ctx *ctx, phmm_workload *w, double *ou
 extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, double *out, phmm_stats *stats)
 {
     if (!ctx || !fb) return PHMM_ERR_ARG;
-    if (fb->n_batches < 0 || (fb->n_batches && (!fb->batch_num_reads || !fb->batch_num_haps))) {
-        ctx->error = "malformed batch table";
-        return PHMM_ERR_ARG;
-    }
-    if ((fb->n_reads > 0 && !fb->read_len) || (fb->n_haps > 0 && !fb->hap_len) || fb->n_reads < 0 || fb->n_haps < 0) {
-        ctx->error = "NULL read / haplotype table";
-        return PHMM_ERR_ARG;
-    }
     const double t_begin = wall_ms();
-    // ---- chunk boundaries (whole batches), by cells --------------------------------------------
-    struct Chunk { int64_t b0, b1, r0, r1, h0, h1, p0, p1; };
     std::vector<Chunk> chunks;
     {
-        std::vector<int64_t> cells((size_t)fb->n_batches, 0);
-        int64_t r = 0, h = 0, total = 0;
-        for (int64_t b = 0; b < fb->n_batches; ++b) {
-            const int nr = fb->batch_num_reads[b], nh = fb->batch_num_haps[b];
-            if (nr < 0 || nh < 0 || r + nr > fb->n_reads || h + nh > fb->n_haps) {
-                ctx->error = "batch tables do not add up to n_reads / n_haps";
-                return PHMM_ERR_ARG;
-            }
-            int64_t sr = 0, sh = 0;
-            for (int k = 0; k < nr; ++k) sr += fb->read_len[r + k];
-            for (int k = 0; k < nh; ++k) sh += fb->hap_len[h + k];
-            cells[b] = sr * sh;
-            total += cells[b];
-            r += nr; h += nh;
-        }
         // default: chunks of >= 1.2e10 cells (a few ms of kernels), at most 12; the first one half
         // that size so the device starts early
-        int64_t per = ctx->chunk_cells > 0 ? ctx->chunk_cells : std::max<int64_t>(12000000000ll, total / 12 + 1);
-        Chunk c{0, 0, 0, 0, 0, 0, 0, 0};
-        int64_t acc = 0;
-        r = 0; h = 0;
-        int64_t p = 0;
-        for (int64_t b = 0; b < fb->n_batches; ++b) {
-            const int nr = fb->batch_num_reads[b], nh = fb->batch_num_haps[b];
-            acc += cells[b];
-            r += nr; h += nh; p += (int64_t)nr * nh;
-            const int64_t want = chunks.empty() ? per / 2 : per;
-            if (acc >= want || b == fb->n_batches - 1) {
-                c.b1 = b + 1; c.r1 = r; c.h1 = h; c.p1 = p;
-                chunks.push_back(c);
-                c = Chunk{b + 1, b + 1, r, r, h, h, p, p};
-                acc = 0;
-            }
-        }
-        if (chunks.empty()) chunks.push_back(Chunk{0, 0, 0, 0, 0, 0, 0, 0});
+        int rc0 = split_batches(ctx, fb, ctx->chunk_cells, 12000000000ll, 12, true, &chunks);
+        if (rc0 != PHMM_OK) return rc0;
     }
     if (chunks.back().p1 > 0 && !out) { ctx->error = "NULL output"; return PHMM_ERR_ARG; }
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -798,11 +818,7 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         if (wl[slot]) rc = retire(j - phmm_ctx::N_SLOTS);      // the slot's arena must be idle
         if (rc != PHMM_OK) break;
         const Chunk &c = chunks[j];
-        phmm_flat_batches sub = *fb;
-        sub.n_batches = c.b1 - c.b0; sub.n_reads = c.r1 - c.r0; sub.n_haps = c.h1 - c.h0;
-        sub.batch_num_reads = fb->batch_num_reads + c.b0; sub.batch_num_haps = fb->batch_num_haps + c.b0;
-        sub.read_len = fb->read_len + c.r0; sub.read_off = fb->read_off + c.r0;
-        sub.hap_len = fb->hap_len + c.h0; sub.hap_off = fb->hap_off + c.h0;
+        phmm_flat_batches sub = sub_batches(fb, c);
         StreamSet &ss = ctx->ss[slot];
         rc = wl_create(ctx, &sub, &ctx->arena[slot], ctx->copy_in, &wl[slot]);
         if (rc != PHMM_OK) break;

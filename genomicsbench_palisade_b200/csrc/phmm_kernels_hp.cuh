@@ -15,8 +15,8 @@
 //     by register-file operand bandwidth (profiles/README.md), so this is what buys speed.
 //   * Scaled recurrence (see phmm_kernels.cuh, "scaled recurrence"): 6 + ceil(KH / 4) / KH packed FP
 //     instructions per row and step.
-//   * Emission factors: per-warp table e[row][code][lane] of floats; two 32-bit LDS per row and
-//     step, one per haplotype run.
+//   * Emission factors: per-warp table e[code][row quad][lane] of float4; one 128-bit LDS per four
+//     rows, step and haplotype run, multiplied in with two scalar FMULs per row.
 //   * Everything else as in phmm_kernels.cuh: right-aligned reads with dummy rows on top, four
 //     columns per loop iteration, separator columns with the reset on the step that ends an
 //     iteration, cp.async-staged haplotype rings (one per run), FP64-rescue and guard lists.
@@ -31,10 +31,10 @@ __device__ __forceinline__ float2 hp_shfl_up(float2 v, int width)
 {
     return make_float2(__shfl_up_sync(FULL_MASK, v.x, 1, width), __shfl_up_sync(FULL_MASK, v.y, 1, width));
 }
-__device__ __forceinline__ float hp_lds(uint32_t addr)
+__device__ __forceinline__ float4 hp_lds128(uint32_t addr)
 {
-    float v;
-    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
     return v;
 }
 
@@ -45,8 +45,10 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
     constexpr int NTOP = (KH + 3) / 4;                 // groups of chained rows per thread
     constexpr int GRP = (KH + NTOP - 1) / NTOP;        // rows per group (<= 4)
     constexpr int ROWS = KH * LANES;
-    constexpr int ELINE = 128;                         // bytes per (row, code) table line
-    constexpr int ETAB = KH * N_CODES * ELINE;
+    constexpr int NQ = (KH + 3) / 4;                   // row quads per thread
+    constexpr int EQUAD = 512;                         // bytes per (code, quad) table line: float4 per lane
+    constexpr int ECODE = NQ * EQUAD;                  // bytes per code
+    constexpr int ETAB = N_CODES * ECODE;
     constexpr int RTAB = (MAX_RUN_HAPS + 2) * 8;       // per run: float iy[], int len[]
     constexpr int WSM = ETAB + 2 * STREAM_RING + 2 * RTAB;
     constexpr uint32_t WMASK = STREAM_RING / 4 - 1;
@@ -62,7 +64,7 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
         iytab[h] = reinterpret_cast<float *>(etab + ETAB + 2 * STREAM_RING + h * RTAB);
         hltab[h] = reinterpret_cast<int32_t *>(iytab[h] + (MAX_RUN_HAPS + 2));
     }
-    const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(etab) + lane * 4;
+    const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(etab) + lane * 16;
     const int gl = lane & (LANES - 1);
     const int grp = lane / LANES;
     const bool last_lane = (gl == LANES - 1);
@@ -138,7 +140,7 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
 #pragma unroll
                 for (int code = 0; code < N_CODES; ++code) {
                     const bool match = (code == rcode) || (code == CODE_N) || (rcode == CODE_N);
-                    *reinterpret_cast<float *>(etab + (p * N_CODES + code) * ELINE + lane * 4) =
+                    *reinterpret_cast<float *>(etab + code * ECODE + (p / 4) * EQUAD + lane * 16 + (p % 4) * 4) =
                         (code == CODE_SEP || rcode < 0) ? 0.0f : (match ? em : ex);
                 }
             }
@@ -223,14 +225,19 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
                 wprev0 = wnext0; wprev1 = wnext1;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    // -- emission factors of this column: table line (row * N_CODES + code) * 128
-                    const uint32_t ea0 = ebase + (((codes0 >> (8 * k)) & 0xffu) << 7);
-                    const uint32_t ea1 = ebase + (((codes1 >> (8 * k)) & 0xffu) << 7);
-                    float2 e[KH];
+                    // -- emission factors of this column: one 128-bit LDS per row quad and run.  The
+                    //    two runs' factors land in unrelated registers, so the emission multiply is
+                    //    two scalar FMULs per row (same FP32-pipe time as one FMUL2) -- the kernel is
+                    //    bound by the operand-read port, where four 32-bit LDS cost four cycles and
+                    //    one 128-bit LDS costs one.
+                    const uint32_t ea0 = ebase + ((codes0 >> (8 * k)) & 0xffu) * ECODE;
+                    const uint32_t ea1 = ebase + ((codes1 >> (8 * k)) & 0xffu) * ECODE;
+                    float e0[NQ * 4], e1[NQ * 4];
 #pragma unroll
-                    for (int p = 0; p < KH; ++p) {
-                        e[p].x = hp_lds(ea0 + p * N_CODES * ELINE);
-                        e[p].y = hp_lds(ea1 + p * N_CODES * ELINE);
+                    for (int q = 0; q < NQ; ++q) {
+                        const float4 v0 = hp_lds128(ea0 + q * EQUAD), v1 = hp_lds128(ea1 + q * EQUAD);
+                        e0[4 * q] = v0.x; e0[4 * q + 1] = v0.y; e0[4 * q + 2] = v0.z; e0[4 * q + 3] = v0.w;
+                        e1[4 * q] = v1.x; e1[4 * q + 1] = v1.y; e1[4 * q + 2] = v1.z; e1[4 * q + 3] = v1.w;
                     }
                     // -- neighbours: bottom row of the upstream lane, one and two steps ago
                     U2m = U1m; U2z = U1z;
@@ -243,7 +250,8 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
                     for (int p = 0; p < KH; ++p) {
                         const float2 dm = p ? M[p ? p - 1 : 0] : U2m;
                         const float2 dz = p ? __ffma2_rn(X[p ? p - 1 : 0], hp_bc(cP[p ? p - 1 : 0]), Y[p ? p - 1 : 0]) : U2z;
-                        nM[p] = __fmul2_rn(__ffma2_rn(dm, hp_bc(cA[p]), dz), e[p]);
+                        const float2 tm = __ffma2_rn(dm, hp_bc(cA[p]), dz);
+                        nM[p] = make_float2(__fmul_rn(tm.x, e0[p]), __fmul_rn(tm.y, e1[p]));
                         nY[p] = __ffma2_rn(M[p], hp_bc(cK3[p]), __fmul2_rn(Y[p], hp_bc(cYY[p])));
                     }
 #pragma unroll

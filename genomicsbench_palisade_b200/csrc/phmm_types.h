@@ -96,9 +96,9 @@ static const int MAX_KH_SCALAR = MAX_KH;      // FP64 rescue classes: 32 lanes x
 // dynamic shared memory per warp: emission table [kh][N_CODES][32 lanes] of 8 bytes, the stream
 // ring, and the per-run haplotype table (INITIAL_CONSTANT / haplen as 8 bytes + length)
 static inline int smem_per_warp(int kh) { return kh * N_CODES * 256 + STREAM_RING + (MAX_RUN_HAPS + 2) * 12; }
-// haplotype-pair kernels: emission table [kh][N_CODES][32 lanes] of 4 bytes, two stream rings, two
+// haplotype-pair kernels: emission table [N_CODES][kh / 4][32 lanes] of 16 bytes, two stream rings, two
 // run tables (float INITIAL_CONSTANT / haplen + int length)
-static inline int smem_per_warp_hp(int kh) { return kh * N_CODES * 128 + 2 * STREAM_RING + 2 * (MAX_RUN_HAPS + 2) * 8; }
+static inline int smem_per_warp_hp(int kh) { return ((kh + 3) / 4) * N_CODES * 512 + 2 * STREAM_RING + 2 * (MAX_RUN_HAPS + 2) * 8; }
 
 template <typename T>
 struct KernelParams {
