@@ -418,7 +418,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     w->resc_total = tot;
     const bool need_resc = (w->precision != 2);   // mode 1 still needs the fast kernel's guard list
 
-    const int64_t pool_len = P.pool_hi - P.pool_lo;
+    const int64_t pool_len = P.pool_len;
     w->pool_stride = (pool_len + 255) & ~(int64_t)255;
     int64_t ntasks = 0, nhtasks = 0;
     for (auto &cp : P.classes) {
@@ -435,7 +435,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
         // also come back as single-haplotype rescue / guard tasks
         const int64_t cols = std::max<int64_t>(P.long_max_cols, P.max_haplen + SEP_COLS) + 64;
         w->scratch_stride = 6 * cols;
-        w->scratch_blocks = ctx->sm_count * 2;
+        w->scratch_blocks = ctx->sm_count * 8 / WARPS_PER_BLOCK;     // eight warps per SM
     }
 
     // ---- one allocation, carved into 256-byte aligned pieces ------------------------------------
@@ -496,10 +496,10 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     } while (0)
     const uint8_t *pools[5] = {fb->rs, fb->q, fb->i, fb->d, fb->c};
     int64_t h2d = 0;
-    if (pool_len > 0)
-        for (int k = 0; k < 5; ++k) {
-            WL_TRY(cudaMemcpyAsync(w->d_pool + k * w->pool_stride, pools[k] + P.pool_lo, (size_t)pool_len, cudaMemcpyHostToDevice, up));
-            h2d += pool_len;
+    for (int k = 0; k < 5; ++k)
+        for (const Plan::Segment &sg : P.segments) {
+            WL_TRY(cudaMemcpyAsync(w->d_pool + k * w->pool_stride + sg.dst, pools[k] + sg.src, (size_t)sg.len, cudaMemcpyHostToDevice, up));
+            h2d += sg.len;
         }
     WL_TRY(cudaMemcpyAsync(w->d_stream, P.stream.data(), P.stream.size(), cudaMemcpyHostToDevice, up));
     WL_TRY(cudaMemcpyAsync(w->d_hap_len, P.hap_len.data(), P.hap_len.size() * sizeof(int32_t), cudaMemcpyHostToDevice, up));
@@ -774,6 +774,7 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
 {
     if (!ctx || !fb) return PHMM_ERR_ARG;
     const double t_begin = wall_ms();
+    static const bool trace = getenv("PHMM_TRACE") != nullptr;
     std::vector<Chunk> chunks;
     {
         // default: chunks of >= 1.2e10 cells (a few ms of kernels), at most 12; the first one half
@@ -820,13 +821,20 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         const Chunk &c = chunks[j];
         phmm_flat_batches sub = sub_batches(fb, c);
         StreamSet &ss = ctx->ss[slot];
+        const double tc0 = wall_ms();
         rc = wl_create(ctx, &sub, &ctx->arena[slot], ctx->copy_in, &wl[slot]);
         if (rc != PHMM_OK) break;
+        const double tc1 = wall_ms();
         if (cudaEventRecord(ss.ev_uploaded, ctx->copy_in) != cudaSuccess) { ctx->error = "cudaEventRecord failed"; rc = PHMM_ERR_CUDA; break; }
         rc = wl_launch(ctx, wl[slot], ss, ss.ev_uploaded);
-        if (j == 0) t_first_launch = wall_ms();
+        const double tc2 = wall_ms();
+        if (j == 0) t_first_launch = tc2;
         // with the next chunk queued, wait for the previous one and fetch its results
         if (rc == PHMM_OK && j >= 1 && wl[(j - 1) % phmm_ctx::N_SLOTS]) rc = retire(j - 1);
+        if (trace)
+            fprintf(stderr, "phmm trace: chunk %zu/%zu batches %lld cells %.3e  plan+upload %.2f ms  launch %.2f ms  retire(prev) %.2f ms  t=%.2f\n",
+                    j, chunks.size(), (long long)(c.b1 - c.b0), (double)wl[slot]->n_cells, tc1 - tc0, tc2 - tc1, wall_ms() - tc2,
+                    wall_ms() - t_begin);
     }
     for (size_t j = chunks.size() >= 2 ? chunks.size() - 2 : 0; j < chunks.size() && rc == PHMM_OK; ++j)
         if (wl[j % phmm_ctx::N_SLOTS]) rc = retire(j);

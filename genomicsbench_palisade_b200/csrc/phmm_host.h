@@ -49,7 +49,11 @@ struct Plan {
     std::vector<int32_t> hap_len;        // stream order, + 1 slack entry
     std::vector<ClassPlan> classes;
     int64_t n_pairs = 0, n_cells = 0;
-    int64_t pool_lo = 0, pool_hi = 0;    // referenced byte range of the read pools
+    // Referenced pieces of the caller's read pools, packed back to back on the device: bytes
+    // [src, src + len) of each of the five pools go to device pool offset dst.
+    struct Segment { int64_t src, len, dst; };
+    std::vector<Segment> segments;
+    int64_t pool_len = 0;                // sum of segment lengths
     int64_t resc_cap[MAX_KH_SCALAR + 1]; // pairs whose read falls in each scalar class
     int max_rslen = 0, max_haplen = 0;
     int long_max_cols = 0;               // longest run handed to a multi-pass kernel (0 = none)

@@ -553,7 +553,7 @@ phmm_forward_kernel(const KernelParams<T> P)
     }
 }
 
-// Minimum resident blocks per SM requested from ptxas (caps registers per thread).
+// Minimum resident groups of four warps per SM requested from ptxas (caps registers per thread).
 template <typename T, int KH>
 struct MinBlocks {
     static constexpr int K = KH * (sizeof(T) / 4);
@@ -564,9 +564,9 @@ typedef void (*KernelF32)(const KernelParams<float>);
 typedef void (*KernelF64)(const KernelParams<double>);
 
 template <int KH, int LANES, bool FAST, bool LONG = false>
-static KernelF32 f32_kernel() { return phmm_forward_kernel<float, KH, LANES, FAST, LONG, MinBlocks<float, KH>::value>; }
+static KernelF32 f32_kernel() { return phmm_forward_kernel<float, KH, LANES, FAST, LONG, MinBlocks<float, KH>::value * (4 / WARPS_PER_BLOCK)>; }
 template <int KH, bool FAST, bool LONG = false>
-static KernelF64 f64_kernel() { return phmm_forward_kernel<double, KH, 32, FAST, LONG, MinBlocks<double, KH>::value>; }
+static KernelF64 f64_kernel() { return phmm_forward_kernel<double, KH, 32, FAST, LONG, MinBlocks<double, KH>::value * (4 / WARPS_PER_BLOCK)>; }
 
 }  // namespace phmm
 #endif

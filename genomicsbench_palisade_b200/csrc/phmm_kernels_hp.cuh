@@ -301,14 +301,14 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
     }
 }
 
-// Minimum resident blocks per SM requested from ptxas (caps registers per thread).
+// Minimum resident groups of four warps per SM requested from ptxas (caps registers per thread).
 template <int KH>
 struct MinBlocksHP {
     static constexpr int value = KH <= 2 ? 6 : KH <= 4 ? 5 : KH <= 6 ? 4 : KH <= 9 ? 3 : 2;
 };
 
 template <int KH, int LANES>
-static KernelF32 f32_hp_kernel() { return phmm_forward_hp_kernel<KH, LANES, MinBlocksHP<KH>::value>; }
+static KernelF32 f32_hp_kernel() { return phmm_forward_hp_kernel<KH, LANES, MinBlocksHP<KH>::value * (4 / WARPS_PER_BLOCK)>; }
 
 }  // namespace phmm
 #endif

@@ -72,19 +72,40 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
     }
     if (nr != fb.n_reads || nh != fb.n_haps) return fail(PHMM_ERR_ARG, "batch tables do not add up to n_reads / n_haps");
     if (nh + 1 >= INT32_MAX) return fail(PHMM_ERR_ARG, "too many haplotypes");
-    int64_t lo = INT64_MAX, hi = 0;
+    bool sorted = true;
     for (int64_t r = 0; r < fb.n_reads; ++r) {
         const int len = fb.read_len[r];
         if (len <= 0) return fail(PHMM_ERR_EMPTY_SEQ, "read of length <= 0 (undefined in the reference)");
         if (len > PHMM_MAX_SEQ_LEN) return fail(PHMM_ERR_TOO_LONG, "read longer than PHMM_MAX_SEQ_LEN");
         if (fb.read_off[r] < 0) return fail(PHMM_ERR_ARG, "negative read offset");
-        lo = std::min(lo, fb.read_off[r]);
-        hi = std::max(hi, fb.read_off[r] + len);
+        if (r && fb.read_off[r] < fb.read_off[r - 1]) sorted = false;
         P.max_rslen = std::max(P.max_rslen, len);
     }
-    if (fb.n_reads == 0) lo = 0;
-    P.pool_lo = lo;
-    P.pool_hi = hi;
+    // ---- pool segments: merge the reads' byte ranges (gaps up to 64 bytes are carried along) so that
+    //      only referenced data is uploaded, whatever else the caller's pools hold ------------------
+    std::vector<int64_t> seg_of_read((size_t)fb.n_reads);
+    {
+        std::vector<int64_t> order;
+        if (!sorted) {
+            order.resize((size_t)fb.n_reads);
+            for (int64_t r = 0; r < fb.n_reads; ++r) order[r] = r;
+            std::sort(order.begin(), order.end(), [&](int64_t x, int64_t y) { return fb.read_off[x] < fb.read_off[y]; });
+        }
+        int64_t dst = 0;
+        for (int64_t k = 0; k < fb.n_reads; ++k) {
+            const int64_t r = sorted ? k : order[k];
+            const int64_t off = fb.read_off[r], end = off + fb.read_len[r];
+            if (P.segments.empty() || off > P.segments.back().src + P.segments.back().len + 64) {
+                if (!P.segments.empty()) dst += (P.segments.back().len + 15) & ~(int64_t)15;
+                P.segments.push_back(Plan::Segment{off, 0, dst});
+            }
+            Plan::Segment &sg = P.segments.back();
+            sg.len = std::max(sg.len, end - sg.src);
+            seg_of_read[r] = (int64_t)P.segments.size() - 1;
+        }
+        if (!P.segments.empty()) dst += P.segments.back().len;
+        P.pool_len = dst;
+    }
     for (int64_t h = 0; h < fb.n_haps; ++h) {
         const int len = fb.hap_len[h];
         if (len <= 0) return fail(PHMM_ERR_EMPTY_SEQ, "haplotype of length <= 0 (division by haplen in the reference)");
@@ -174,7 +195,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
             for (int k = 0; k < bnr; ++k) {
                 const int64_t r = r0 + k;
                 ReadRec &rr = P.reads[r];
-                rr.off = fb.read_off[r] - P.pool_lo;
+                rr.off = fb.read_off[r] - P.segments[seg_of_read[r]].src + P.segments[seg_of_read[r]].dst;
                 rr.len = fb.read_len[r];
                 rr.batch = (int32_t)b;
                 rr.out_base = out0 + (int64_t)k * bnh;

@@ -87,7 +87,8 @@ static const int MAX_RUN_HAPS = 62;           // haplotypes per run: per-warp ta
 static const int STREAM_CHUNK = 512;          // haplotype-stream bytes staged per cp.async round
 static const int STREAM_RING = 2048;          // per-warp shared-memory ring (4 chunks)
 static const int STREAM_SLACK = 2 * STREAM_CHUNK + 128;   // readable bytes past the last column
-static const int WARPS_PER_BLOCK = 4;
+static const int WARPS_PER_BLOCK = 1;          // one warp per block: a persistent block frees its SM slot as soon as its
+                                               // warp runs out of tasks, so the next kernel's blocks fill the tail
 static const int MAX_KH = 8;                  // single-pass classes: kh <= 8 (255 rows at 32 lanes)
 static const int MAX_KH_HP = 16;              // haplotype-pair classes: kh <= 16 (511 rows at 32 lanes)
 static const int LONG_KH = 8;                 // register tile of the multi-pass kernels

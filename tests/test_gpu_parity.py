@@ -134,6 +134,16 @@ def test_host_entry_point_pipelines_chunks():
             assert st["n_pairs"] == fb.n_pairs and st["n_cells"] == fb.n_cells
             assert st["n_rescued"] == int(ref.rescued.sum())
     assert same_or_close(res[0][ref.rescued == 0], ref.out[ref.rescued == 0], RTOL_FP32)
+    # a shard that references scattered, out-of-order pieces of shared pools (what the driver hands each
+    # GPU): only the referenced segments are uploaded
+    sub = fb.select_batches(np.array([19, 2, 11, 4, 3]))
+    rs = oracle.run_port(sub)
+    eng = phmm.PairHMM(chunk_cells=1_000_000)
+    out, st = eng.compute(sub, stats=True)
+    eng.close()
+    r = rs.rescued.astype(bool)
+    assert same_or_close(out[~r], rs.out[~r], RTOL_FP32) and same_or_close(out[r], rs.out[r], RTOL_FP64)
+    assert st["h2d_bytes"] < 5 * int(sub.read_len.sum()) + 64 * len(sub.read_len) + int(sub.hap_len.sum()) * 2 + 200_000
 
 
 def test_random_workloads_against_the_oracle():
