@@ -69,8 +69,8 @@ struct phmm_ctx {
     int device = 0;
     int sm_count = 0;
     // slot 0 also serves the device-resident workload API; the host-buffer entry points pipeline
-    // chunks of batches through both slots (plan + upload of one chunk under the kernels of the other)
-    static const int N_SLOTS = 2;
+    // chunks of batches through all slots (plan + upload of one chunk under the kernels of the others)
+    static const int N_SLOTS = 3;
     StreamSet ss[N_SLOTS];
     Arena arena[N_SLOTS];
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
@@ -304,9 +304,9 @@ namespace {
 // A range of whole batches of a phmm_flat_batches and the reads / haplotypes / pairs it spans.
 struct Chunk { int64_t b0, b1, r0, r1, h0, h1, p0, p1; };
 
-// Cuts the batches into consecutive chunks of about `per` cells (0: max(min_cells, total / max_chunks)).
-int split_batches(phmm_ctx *ctx, const phmm_flat_batches *fb, int64_t per, int64_t min_cells, int max_chunks,
-                  bool small_first, std::vector<Chunk> *out)
+// Cuts the batches into consecutive chunks of about `per` cells (0: total / n_chunks clamped to [min_cells, max_cells]).
+int split_batches(phmm_ctx *ctx, const phmm_flat_batches *fb, int64_t per, int64_t min_cells, int64_t max_cells,
+                  int n_chunks, bool small_first, std::vector<Chunk> *out)
 {
     std::vector<Chunk> &chunks = *out;
     chunks.clear();
@@ -325,7 +325,7 @@ int split_batches(phmm_ctx *ctx, const phmm_flat_batches *fb, int64_t per, int64
         total += cells[b];
         r += nr; h += nh;
     }
-    if (per <= 0) per = std::max<int64_t>(min_cells, total / max_chunks + 1);
+    if (per <= 0) per = std::max<int64_t>(min_cells, std::min<int64_t>(max_cells, total / n_chunks + 1));
     Chunk c{0, 0, 0, 0, 0, 0, 0, 0};
     int64_t acc = 0, p = 0;
     r = 0; h = 0;
@@ -777,15 +777,16 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
     static const bool trace = getenv("PHMM_TRACE") != nullptr;
     std::vector<Chunk> chunks;
     {
-        // default: chunks of >= 1.2e10 cells (a few ms of kernels), at most 12; the first one half
-        // that size so the device starts early
-        int rc0 = split_batches(ctx, fb, ctx->chunk_cells, 12000000000ll, 12, true, &chunks);
+        // default: a tenth of the work per chunk, between 4e9 and 2.4e10 cells (1 to 6 ms of kernels:
+        // smaller chunks run the device less efficiently, larger ones expose more of the first
+        // plan + upload); the first one half that size so the device starts early
+        int rc0 = split_batches(ctx, fb, ctx->chunk_cells, 4000000000ll, 24000000000ll, 10, true, &chunks);
         if (rc0 != PHMM_OK) return rc0;
     }
     if (chunks.back().p1 > 0 && !out) { ctx->error = "NULL output"; return PHMM_ERR_ARG; }
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
 
-    phmm_workload *wl[phmm_ctx::N_SLOTS] = {nullptr, nullptr};
+    phmm_workload *wl[phmm_ctx::N_SLOTS] = {};
     phmm_stats agg;
     memset(&agg, 0, sizeof agg);
     int rc = PHMM_OK;
@@ -805,6 +806,9 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         int r2 = wl_finish(ctx, w, ss, &s);
         ms_d2h += wall_ms() - t0;
         if (r2 != PHMM_OK) return r2;
+        if (trace)
+            fprintf(stderr, "phmm trace:   chunk %zu done: fp32 %.2f ms fp64 %.2f ms total %.2f ms, %d launches, %lld tasks, t=%.2f\n", j,
+                    s.ms_fp32, s.ms_fp64, s.ms_total, s.n_launches, (long long)s.n_tasks, wall_ms() - t_begin);
         agg.n_pairs += s.n_pairs; agg.n_cells += s.n_cells; agg.n_rescued += s.n_rescued;
         agg.n_guard += s.n_guard; agg.n_tasks += s.n_tasks; agg.h2d_bytes += s.h2d_bytes;
         agg.n_launches += s.n_launches; agg.n_classes = std::max(agg.n_classes, s.n_classes);
@@ -816,7 +820,8 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
     };
     for (size_t j = 0; j < chunks.size() && rc == PHMM_OK; ++j) {
         const int slot = (int)(j % phmm_ctx::N_SLOTS);
-        if (wl[slot]) rc = retire(j - phmm_ctx::N_SLOTS);      // the slot's arena must be idle
+        // the slot's arena must be idle: wait for the chunk that used it and fetch its results
+        if (wl[slot]) rc = retire(j - phmm_ctx::N_SLOTS);
         if (rc != PHMM_OK) break;
         const Chunk &c = chunks[j];
         phmm_flat_batches sub = sub_batches(fb, c);
@@ -829,14 +834,13 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         rc = wl_launch(ctx, wl[slot], ss, ss.ev_uploaded);
         const double tc2 = wall_ms();
         if (j == 0) t_first_launch = tc2;
-        // with the next chunk queued, wait for the previous one and fetch its results
-        if (rc == PHMM_OK && j >= 1 && wl[(j - 1) % phmm_ctx::N_SLOTS]) rc = retire(j - 1);
         if (trace)
-            fprintf(stderr, "phmm trace: chunk %zu/%zu batches %lld cells %.3e  plan+upload %.2f ms  launch %.2f ms  retire(prev) %.2f ms  t=%.2f\n",
+            fprintf(stderr, "phmm trace: chunk %zu/%zu batches %lld cells %.3e  plan+upload %.2f ms  launch %.2f ms  (waited %.2f ms)  t=%.2f\n",
                     j, chunks.size(), (long long)(c.b1 - c.b0), (double)wl[slot]->n_cells, tc1 - tc0, tc2 - tc1, wall_ms() - tc2,
                     wall_ms() - t_begin);
     }
-    for (size_t j = chunks.size() >= 2 ? chunks.size() - 2 : 0; j < chunks.size() && rc == PHMM_OK; ++j)
+    for (size_t j = chunks.size() > (size_t)phmm_ctx::N_SLOTS ? chunks.size() - phmm_ctx::N_SLOTS : 0;
+         j < chunks.size() && rc == PHMM_OK; ++j)
         if (wl[j % phmm_ctx::N_SLOTS]) rc = retire(j);
     if (rc != PHMM_OK) {
         cudaDeviceSynchronize();
