@@ -1,0 +1,153 @@
+// GATK native-bindings shaped batch API on top of the context.
+//
+// Mirrors IntelPairHmm.initNative / computeLikelihoodsNative / doneNative
+// (tools/GKL/src/main/native/pairhmm/IntelPairHmm.cc:32-96,103-156,164-168): one call = all reads x
+// all haplotypes of an active region, results read-major (JavaData.h:44-68), FP32 with FP64 rescue
+// or -- with use_double -- FP64 for every pair (:123-124).  Host-only translation unit: the work
+// is done by phmm_compute_flat.
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "phmm_host.h"
+
+struct phmm_gatk {
+    phmm_ctx *ctx = nullptr;
+    int use_double = 0, max_threads = 1;
+    std::string error;
+    // scratch reused across calls (GATK calls once per active region, tens of thousands of times)
+    phmm::ParsedBatches b;
+    std::vector<double> out;
+};
+
+namespace {
+thread_local std::string g_gatk_create_error;
+
+void clear(phmm::ParsedBatches &b)
+{
+    b.batch_num_reads.clear(); b.batch_num_haps.clear();
+    b.read_len.clear(); b.read_off.clear(); b.hap_len.clear(); b.hap_off.clear();
+    b.rs.clear(); b.q.clear(); b.i.clear(); b.d.clear(); b.c.clear(); b.hap.clear();
+}
+
+int append_region(phmm_gatk *g, const phmm_gatk_read *reads, int32_t n_reads, const phmm_gatk_hap *haps,
+                  int32_t n_haps)
+{
+    phmm::ParsedBatches &b = g->b;
+    if (n_reads < 0 || n_haps < 0 || (n_reads && !reads) || (n_haps && !haps)) {
+        g->error = "negative count or NULL array";
+        return PHMM_ERR_ARG;
+    }
+    b.batch_num_reads.push_back(n_reads);
+    b.batch_num_haps.push_back(n_haps);
+    for (int32_t r = 0; r < n_reads; ++r) {
+        const phmm_gatk_read &rd = reads[r];
+        if (rd.length <= 0) { g->error = "readBases of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+        if (rd.length > PHMM_MAX_SEQ_LEN) { g->error = "read longer than PHMM_MAX_SEQ_LEN"; return PHMM_ERR_TOO_LONG; }
+        if (!rd.readBases || !rd.readQuals || !rd.insertionGOP || !rd.deletionGOP || !rd.overallGCP) {
+            g->error = "NULL field in ReadDataHolder";
+            return PHMM_ERR_ARG;
+        }
+        b.read_len.push_back(rd.length);
+        b.read_off.push_back((int64_t)b.rs.size());
+        b.rs.insert(b.rs.end(), rd.readBases, rd.readBases + rd.length);
+        b.q.insert(b.q.end(), rd.readQuals, rd.readQuals + rd.length);
+        b.i.insert(b.i.end(), rd.insertionGOP, rd.insertionGOP + rd.length);
+        b.d.insert(b.d.end(), rd.deletionGOP, rd.deletionGOP + rd.length);
+        b.c.insert(b.c.end(), rd.overallGCP, rd.overallGCP + rd.length);
+    }
+    for (int32_t h = 0; h < n_haps; ++h) {
+        const phmm_gatk_hap &hp = haps[h];
+        if (hp.length <= 0) { g->error = "haplotypeBases of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+        if (hp.length > PHMM_MAX_SEQ_LEN) { g->error = "haplotype longer than PHMM_MAX_SEQ_LEN"; return PHMM_ERR_TOO_LONG; }
+        if (!hp.haplotypeBases) { g->error = "NULL haplotypeBases"; return PHMM_ERR_ARG; }
+        b.hap_len.push_back(hp.length);
+        b.hap_off.push_back((int64_t)b.hap.size());
+        b.hap.insert(b.hap.end(), hp.haplotypeBases, hp.haplotypeBases + hp.length);
+    }
+    return PHMM_OK;
+}
+}  // namespace
+
+extern "C" const char *phmm_gatk_last_error(const phmm_gatk *g)
+{
+    return g ? g->error.c_str() : g_gatk_create_error.c_str();
+}
+
+extern "C" phmm_ctx *phmm_gatk_context(phmm_gatk *g) { return g ? g->ctx : nullptr; }
+
+extern "C" int phmm_gatk_init(int device, int use_double, int max_threads, int use_fpga, phmm_gatk **out)
+{
+    if (!out) return PHMM_ERR_ARG;
+    *out = nullptr;
+    if (use_fpga) {
+        // the reference only consults the FPGA when shacc_pairhmm::calculate succeeds, which the
+        // shipped stub never does (shacc_pairhmm.h); there is nothing to mirror
+        g_gatk_create_error = "use_fpga is not supported";
+        return PHMM_ERR_ARG;
+    }
+    phmm_ctx *ctx = nullptr;
+    int rc = phmm_create(device, &ctx);
+    if (rc != PHMM_OK) { g_gatk_create_error = phmm_last_error(nullptr); return rc; }
+    // computeLikelihoodsNative's policy: FP32 then FP64 below MIN_ACCEPTED, or FP64 only
+    phmm_set_option(ctx, PHMM_OPT_PRECISION, use_double ? 2 : 0);
+    phmm_set_option(ctx, PHMM_OPT_FP32_KERNEL, 1);
+    phmm_gatk *g = new phmm_gatk();
+    g->ctx = ctx;
+    g->use_double = use_double ? 1 : 0;
+    g->max_threads = max_threads;
+    *out = g;
+    return PHMM_OK;
+}
+
+extern "C" int phmm_gatk_compute_regions(phmm_gatk *g, const phmm_gatk_region *regions, int64_t n_regions)
+{
+    if (!g || n_regions < 0 || (n_regions && !regions)) return PHMM_ERR_ARG;
+    clear(g->b);
+    int64_t npairs = 0;
+    for (int64_t k = 0; k < n_regions; ++k) {
+        const phmm_gatk_region &rg = regions[k];
+        int rc = append_region(g, rg.reads, rg.n_reads, rg.haps, rg.n_haps);
+        if (rc != PHMM_OK) return rc;
+        const int64_t n = (int64_t)rg.n_reads * rg.n_haps;
+        if (n && !rg.likelihoods) { g->error = "NULL likelihoods"; return PHMM_ERR_ARG; }
+        npairs += n;
+    }
+    if (npairs == 0) return PHMM_OK;
+    g->b.finish();
+    double *dst = g->out.data();
+    if (n_regions == 1) {
+        dst = regions[0].likelihoods;          // straight into the caller's array
+    } else {
+        g->out.resize((size_t)npairs);
+        dst = g->out.data();
+    }
+    int rc = phmm_compute_flat(g->ctx, &g->b.view, dst, nullptr);
+    if (rc != PHMM_OK) { g->error = phmm_last_error(g->ctx); return rc; }
+    if (n_regions > 1) {
+        int64_t p = 0;
+        for (int64_t k = 0; k < n_regions; ++k) {
+            const int64_t n = (int64_t)regions[k].n_reads * regions[k].n_haps;
+            if (n) memcpy(regions[k].likelihoods, dst + p, (size_t)n * sizeof(double));
+            p += n;
+        }
+    }
+    return PHMM_OK;
+}
+
+extern "C" int phmm_gatk_compute_likelihoods(phmm_gatk *g, const phmm_gatk_read *reads, int32_t n_reads,
+                                             const phmm_gatk_hap *haps, int32_t n_haps, double *likelihoods)
+{
+    phmm_gatk_region rg;
+    rg.reads = reads; rg.haps = haps; rg.likelihoods = likelihoods;
+    rg.n_reads = n_reads; rg.n_haps = n_haps;
+    return phmm_gatk_compute_regions(g, &rg, 1);
+}
+
+extern "C" int phmm_gatk_done(phmm_gatk *g)
+{
+    if (!g) return PHMM_OK;
+    phmm_destroy(g->ctx);
+    delete g;
+    return PHMM_OK;
+}

@@ -95,7 +95,11 @@ struct ParsedBatches {
 }  // namespace phmm
 
 struct phmm_parsed {
-    phmm::ParsedBatches b;
+    phmm::ParsedBatches b;           // owns the data when parsed from text ...
+    void *map = nullptr;             // ... or b.view points into this mapping (phmm_cache_open)
+    size_t map_len = 0;
+    std::vector<double> expected;    // phmm_testdata_*: expected log10 likelihood per pair
+    ~phmm_parsed();
 };
 
 #endif

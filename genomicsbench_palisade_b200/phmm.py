@@ -58,7 +58,10 @@ EXPORTS = ["phmm_abi_version", "phmm_device_count", "phmm_create", "phmm_destroy
            "phmm_compute_flat", "phmm_workload_create", "phmm_workload_run", "phmm_workload_results",
            "phmm_workload_destroy", "phmm_partition_lpt", "phmm_parse_file", "phmm_parse_buffer",
            "phmm_parsed_batches", "phmm_parsed_free", "phmm_microbench", "phmm_get_tables",
-           "phmm_plan_summary"]
+           "phmm_plan_summary", "phmm_cache_write", "phmm_cache_open", "phmm_gatk_init",
+           "phmm_gatk_compute_likelihoods", "phmm_gatk_compute_regions", "phmm_gatk_done",
+           "phmm_gatk_last_error", "phmm_gatk_context", "phmm_testdata_parse_buffer",
+           "phmm_testdata_parse_file", "phmm_testdata_expected"]
 LEGACY_EXPORTS = ["_Z11initPairHMMv", "_Z22computelikelihoodsbothP8testcasePdi",
                   "_Z23computelikelihoodsfloatP8testcasePf", "_Z24computelikelihoodsdoubleP8testcasePd",
                   "_ZN11ConvertChar15conversionTableE"]
@@ -81,6 +84,13 @@ def load_library():
         lib.phmm_parsed_batches.argtypes = [C.c_void_p]
         lib.phmm_parsed_free.argtypes = [C.c_void_p]
         lib.phmm_parsed_free.restype = None
+        lib.phmm_gatk_last_error.restype = C.c_char_p
+        lib.phmm_gatk_last_error.argtypes = [C.c_void_p]
+        lib.phmm_gatk_context.restype = C.c_void_p
+        lib.phmm_gatk_context.argtypes = [C.c_void_p]
+        lib.phmm_gatk_done.argtypes = [C.c_void_p]
+        lib.phmm_testdata_expected.restype = C.c_int64
+        lib.phmm_testdata_expected.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         _lib = lib
     return _lib
 
@@ -133,6 +143,126 @@ def parse_text(data: bytes) -> FlatBatches:
         return flat_from_c(lib.phmm_parsed_batches(h).contents)
     finally:
         lib.phmm_parsed_free(h)
+
+
+def cache_write(fb: FlatBatches, path: str) -> None:
+    """phmm_cache_write: the binary cache of packed batches (no device needed)."""
+    lib = load_library()
+    keep = _Keep(fb)
+    err = C.create_string_buffer(256)
+    rc = lib.phmm_cache_write(C.byref(keep.c), os.fsencode(path), err, C.c_size_t(256))
+    if rc:
+        raise PhmmError(rc, err.value.decode())
+
+
+def cache_open(path: str) -> FlatBatches:
+    """phmm_cache_open (mmap + checksums), copied out into numpy arrays."""
+    lib = load_library()
+    h = C.c_void_p()
+    err = C.create_string_buffer(256)
+    rc = lib.phmm_cache_open(os.fsencode(path), C.byref(h), err, C.c_size_t(256))
+    if rc:
+        raise PhmmError(rc, err.value.decode())
+    try:
+        return flat_from_c(lib.phmm_parsed_batches(h).contents)
+    finally:
+        lib.phmm_parsed_free(h)
+
+
+def parse_testdata(data: bytes):
+    """GATK regression-vector lines (PairHmmUnitTest.java:166-185) -> (1 x 1 batches, expected)."""
+    lib = load_library()
+    h = C.c_void_p()
+    err = C.create_string_buffer(256)
+    rc = lib.phmm_testdata_parse_buffer(data, C.c_size_t(len(data)), C.byref(h), err, C.c_size_t(256))
+    if rc:
+        raise PhmmError(rc, err.value.decode())
+    try:
+        n = lib.phmm_testdata_expected(h, None, 0)
+        exp = np.zeros(max(1, n), np.float64)
+        lib.phmm_testdata_expected(h, _ptr(exp), n)
+        return flat_from_c(lib.phmm_parsed_batches(h).contents), exp[:n]
+    finally:
+        lib.phmm_parsed_free(h)
+
+
+class CGatkRead(C.Structure):
+    _fields_ = [("readBases", C.c_void_p), ("readQuals", C.c_void_p), ("insertionGOP", C.c_void_p),
+                ("deletionGOP", C.c_void_p), ("overallGCP", C.c_void_p), ("length", C.c_int32)]
+
+
+class CGatkHap(C.Structure):
+    _fields_ = [("haplotypeBases", C.c_void_p), ("length", C.c_int32)]
+
+
+class CGatkRegion(C.Structure):
+    _fields_ = [("reads", C.c_void_p), ("haps", C.c_void_p), ("likelihoods", C.c_void_p),
+                ("n_reads", C.c_int32), ("n_haps", C.c_int32)]
+
+
+class GatkPairHMM:
+    """IntelPairHmm.initialize / computeLikelihoods / done (IntelPairHmm.java:75-125) over
+    phmm_gatk_*.  A read is a 5-tuple of bytes objects (readBases, readQuals, insertionGOP,
+    deletionGOP, overallGCP) with raw Phred values, a haplotype a bytes object."""
+
+    def __init__(self, device: int = 0, use_double: bool = False, max_threads: int = 1):
+        self.lib = load_library()
+        self._h = C.c_void_p()
+        rc = self.lib.phmm_gatk_init(C.c_int(device), C.c_int(int(use_double)), C.c_int(max_threads),
+                                     C.c_int(0), C.byref(self._h))
+        if rc:
+            raise PhmmError(rc, (self.lib.phmm_gatk_last_error(None) or b"").decode())
+
+    def _check(self, rc):
+        if rc:
+            raise PhmmError(rc, (self.lib.phmm_gatk_last_error(self._h) or b"").decode())
+
+    @staticmethod
+    def _holders(reads, haps, keep):
+        cr = (CGatkRead * max(1, len(reads)))()
+        for k, rd in enumerate(reads):
+            bufs = [C.create_string_buffer(bytes(x), len(x)) if len(x) else C.create_string_buffer(1) for x in rd]
+            keep.extend(bufs)
+            cr[k] = CGatkRead(*[C.cast(b, C.c_void_p) for b in bufs], len(rd[0]))
+        ch = (CGatkHap * max(1, len(haps)))()
+        for k, hp in enumerate(haps):
+            b = C.create_string_buffer(bytes(hp), len(hp)) if len(hp) else C.create_string_buffer(1)
+            keep.append(b)
+            ch[k] = CGatkHap(C.cast(b, C.c_void_p), len(hp))
+        keep.extend([cr, ch])
+        return cr, ch
+
+    def compute_likelihoods(self, reads, haps) -> np.ndarray:
+        keep = []
+        cr, ch = self._holders(reads, haps, keep)
+        out = np.zeros(max(1, len(reads) * len(haps)), np.float64)
+        self._check(self.lib.phmm_gatk_compute_likelihoods(self._h, cr, C.c_int32(len(reads)), ch,
+                                                           C.c_int32(len(haps)), _ptr(out)))
+        return out[:len(reads) * len(haps)]
+
+    def compute_regions(self, regions):
+        """regions: list of (reads, haps); one library call for all of them."""
+        keep, outs = [], []
+        cg = (CGatkRegion * max(1, len(regions)))()
+        for k, (reads, haps) in enumerate(regions):
+            cr, ch = self._holders(reads, haps, keep)
+            out = np.zeros(max(1, len(reads) * len(haps)), np.float64)
+            outs.append(out)
+            cg[k] = CGatkRegion(C.cast(cr, C.c_void_p), C.cast(ch, C.c_void_p), out.ctypes.data,
+                                len(reads), len(haps))
+        self._check(self.lib.phmm_gatk_compute_regions(self._h, cg, C.c_int64(len(regions))))
+        return [o[:len(r) * len(h)] for o, (r, h) in zip(outs, regions)]
+
+    def done(self):
+        if self._h:
+            self.lib.phmm_gatk_done(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.done()
+        except Exception:
+            pass
 
 
 def partition_lpt(cost, parts: int) -> np.ndarray:

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define PHMM_ABI_VERSION 2
+#define PHMM_ABI_VERSION 3
 
 /* ---- status codes (the reference defines none: it asserts / exit(0)s) ---- */
 #define PHMM_OK              0
@@ -182,6 +182,74 @@ int phmm_parse_file(const char *path, phmm_parsed **out, char *err, size_t err_l
 int phmm_parse_buffer(const char *data, size_t len, phmm_parsed **out, char *err, size_t err_len);
 const phmm_flat_batches *phmm_parsed_batches(const phmm_parsed *p);
 void phmm_parsed_free(phmm_parsed *p);
+
+/* ---- binary cache of parsed batches ----------------------------------------
+ * At GPU speed the text parse dominates the wall time of the reference driver's untimed phase
+ * (read_testfile, PairHMMUnitTest_orig.cpp:186-213).  phmm_cache_write stores flat batches as the
+ * library consumes them: a 128-byte header, then the offset tables and the six byte pools as
+ * 64-byte aligned little-endian sections, quality pools already normalised.  phmm_cache_open
+ * maps the file (no copy, no parse; pages fault in as the planner / uploads touch them) and
+ * checks magic, version, section bounds and a 64-bit FNV-1a checksum of every section; the
+ * handle is released with phmm_parsed_free like a parsed text file. */
+int phmm_cache_write(const phmm_flat_batches *fb, const char *path, char *err, size_t err_len);
+int phmm_cache_open(const char *path, phmm_parsed **out, char *err, size_t err_len);
+
+/* ---- GATK native-bindings shaped batch API -------------------------------
+ * The upstream caller of this kernel: IntelPairHmm.initNative / computeLikelihoodsNative /
+ * doneNative (tools/GKL/src/main/native/pairhmm/IntelPairHmm.cc:32-96,103-156,164-168; Java side
+ * tools/GKL/src/main/java/com/intel/gkl/pairhmm/IntelPairHmm.java:112-117).  One call evaluates
+ * all reads x all haplotypes of an active region; likelihoods[r * n_haps + h] is the log10
+ * likelihood (JavaData.h:44-68 builds the testcases read-major).  Field names are those of GATK's
+ * ReadDataHolder / HaplotypeDataHolder (JavaData.h:15-20); quality bytes are raw Phred values
+ * (no +33), masked & 127 by the kernel as in avx-pairhmm-template.h:110-112,125.
+ *   use_double  : the reference skips the FP32 pass and computes every pair in FP64
+ *                 (IntelPairHmm.cc:123-124: result_float = 0.0f < MIN_ACCEPTED).
+ *   max_threads : host threads of the reference's OpenMP loop; accepted and ignored.
+ *   use_fpga    : the reference's FPGA hook (shacc_pairhmm::calculate, always false); must be 0.
+ * FTZ: initNative turns on x86 flush-to-zero (:66-70).  The kernels here honour denormals, which
+ * changes a result only when an FP32 intermediate falls below 2^-126 (the pair is then far below
+ * MIN_ACCEPTED = 1e-28f or the lost term is < 2^-50 of the sum) or an FP64 intermediate below
+ * 2^-1022 (likelihood < 1e-614); tests/test_oracle.py checks the reference with FTZ on against
+ * FTZ off on the test sets. */
+typedef struct {
+    const uint8_t *readBases, *readQuals, *insertionGOP, *deletionGOP, *overallGCP;
+    int32_t length;
+} phmm_gatk_read;
+
+typedef struct {
+    const uint8_t *haplotypeBases;
+    int32_t length;
+} phmm_gatk_hap;
+
+typedef struct {                        /* one active region = one computeLikelihoodsNative call */
+    const phmm_gatk_read *reads;
+    const phmm_gatk_hap *haps;
+    double *likelihoods;                /* n_reads * n_haps, caller-owned */
+    int32_t n_reads, n_haps;
+} phmm_gatk_region;
+
+typedef struct phmm_gatk phmm_gatk;
+int phmm_gatk_init(int device, int use_double, int max_threads, int use_fpga, phmm_gatk **out);
+int phmm_gatk_compute_likelihoods(phmm_gatk *g, const phmm_gatk_read *reads, int32_t n_reads,
+                                  const phmm_gatk_hap *haps, int32_t n_haps, double *likelihoods);
+/* Many regions in one call: the regions are planned and launched together, which is what makes
+ * a GPU worthwhile when a region holds only tens of reads. */
+int phmm_gatk_compute_regions(phmm_gatk *g, const phmm_gatk_region *regions, int64_t n_regions);
+int phmm_gatk_done(phmm_gatk *g);
+const char *phmm_gatk_last_error(const phmm_gatk *g);
+phmm_ctx *phmm_gatk_context(phmm_gatk *g);    /* the underlying context (options, statistics) */
+
+/* ---- GATK regression-vector loader ------------------------------------------
+ * Parses the line format of GATK's pairhmm-testdata.txt as the reference's dataFileTest reads it
+ * (tools/GKL/src/test/java/com/intel/gkl/pairhmm/PairHmmUnitTest.java:150-197): one pair per line,
+ *     <hap-bases> <read-bases> <read-quals> <ins-quals> <del-quals> <gcp-quals> <expected>
+ * lines starting with '#' are skipped, quality strings are Phred+33 ASCII and are converted as
+ * the test does (normalize(): byte - 33, read quals floored at 6; :174-177,:268-278).  Each line becomes a
+ * 1 x 1 batch; expected[k] receives the expected log10 likelihood of line k.
+ * phmm_testdata_expected returns n (= number of pairs) and copies min(n, cap) values. */
+int phmm_testdata_parse_buffer(const char *data, size_t len, phmm_parsed **out, char *err, size_t err_len);
+int phmm_testdata_parse_file(const char *path, phmm_parsed **out, char *err, size_t err_len);
+int64_t phmm_testdata_expected(const phmm_parsed *p, double *expected, int64_t cap);
 
 /* ---- measurement helpers ----------------------------------------------------------------------
  * FP32 pipe microbenchmarks on the context's device, for the roofline denominator

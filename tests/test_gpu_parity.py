@@ -248,6 +248,78 @@ def test_fast_kernel_with_exotic_gap_penalties():
     assert guard_total > 0      # at least one case must have exercised the overflow path
 
 
+def _regions(fb):
+    """FlatBatches -> [(reads, haps)] in the GATK holder shape (bytes objects, raw Phred values)."""
+    brs, bhs = fb.batch_read_start, fb.batch_hap_start
+    regs = []
+    for b in range(fb.n_batches):
+        reads = []
+        for r in range(brs[b], brs[b + 1]):
+            o, n = int(fb.read_off[r]), int(fb.read_len[r])
+            reads.append(tuple(getattr(fb, f)[o:o + n].tobytes() for f in ("rs", "q", "i", "d", "c")))
+        haps = [fb.hap[int(fb.hap_off[h]):int(fb.hap_off[h]) + int(fb.hap_len[h])].tobytes()
+                for h in range(bhs[b], bhs[b + 1])]
+        regs.append((reads, haps))
+    return regs
+
+
+def test_gatk_shaped_api():
+    # IntelPairHmm.computeLikelihoods (IntelPairHmm.cc:103-156): all reads x all haplotypes, read-major
+    for use_double in (False, True):
+        g = phmm.GatkPairHMM(use_double=use_double)
+        # the reference's known-answer test through this entry (PairHmmUnitTest.java:42-55): raw
+        # (un-normalised) '+' bytes, tolerance 1e-5
+        kat = g.compute_likelihoods([(b"ACGT", b"++++", b"++++", b"++++", b"++++")], [b"ACGT"])
+        assert abs(kat[0] - (-6.022797e-01)) < 1e-5
+        fb = synth.generic(91, 9, (1, 30), (1, 12), (10, 260), (20, 500), q_rng=(6, 45), subst=0.05, foreign_frac=0.25)
+        ref = oracle.run_port(fb, mode=2 if use_double else 0)
+        regs = _regions(fb)
+        one_by_one = np.concatenate([g.compute_likelihoods(r, h) for r, h in regs])
+        together = np.concatenate(g.compute_regions(regs))
+        assert np.array_equal(one_by_one, together)
+        if use_double:
+            assert same_or_close(together, ref.out, RTOL_FP64)
+        else:
+            r = ref.rescued.astype(bool)
+            assert r.any() and (~r).any()
+            assert same_or_close(together[~r], ref.out[~r], RTOL_FP32) and same_or_close(together[r], ref.out[r], RTOL_FP64)
+        # empty region, and the errors the reference leaves undefined
+        assert len(g.compute_likelihoods([], [b"ACGT"])) == 0
+        with pytest.raises(phmm.PhmmError) as e:
+            g.compute_likelihoods([(b"", b"", b"", b"", b"")], [b"ACGT"])
+        assert e.value.code == 2
+        g.done()
+    with pytest.raises(phmm.PhmmError):
+        lib = phmm.load_library()
+        h = C.c_void_p()
+        rc = lib.phmm_gatk_init(0, 0, 1, 1, C.byref(h))          # use_fpga
+        raise phmm.PhmmError(rc, "use_fpga") if rc else AssertionError("use_fpga accepted")
+
+
+def test_driver_cli_with_binary_cache(tmp_path):
+    # the rewritten driver: text input, then the same input mapped from its binary cache
+    import os
+    import subprocess
+    from conftest import ROOT
+    fb = synth.generic(5, 6, (2, 12), (1, 6), (20, 200), (30, 400), q_rng=(6, 45), foreign_frac=0.2)
+    ref = oracle.run_port(fb)
+    path = str(tmp_path / "in.txt")
+    open(path, "wb").write(fb.to_text())
+    exe = os.path.join(ROOT, "genomicsbench_palisade_b200", "phmm")
+    outs = []
+    for args in (["-p"], ["-p", "-c"], ["-p", "-c"]):
+        pr = subprocess.run([exe, "-f", path] + args, capture_output=True, text=True, timeout=300)
+        assert pr.returncode == 0, pr.stderr
+        lines = pr.stdout.strip().split("\n")
+        assert lines[-1].startswith("PairHMM completed. Kernel runtime:")
+        outs.append((np.array([float(x) for x in lines[:-1]]), pr.stderr))
+    assert os.path.exists(path + ".phmmsoa")
+    assert "parsed from text" in outs[1][1] and "mapped from cache" in outs[2][1]
+    for o, _ in outs:
+        assert len(o) == fb.n_pairs and np.allclose(o, ref.out, rtol=1e-4, atol=2e-6)     # "%lf": 6 decimals
+    assert np.array_equal(outs[0][0], outs[2][0])
+
+
 def test_full_size_properties():
     """BASELINE config 2 at full size (2 M pairs): size-independent checks instead of the oracle."""
     fb = synth.c2_large()

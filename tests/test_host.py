@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     # the reference's own C++-linkage symbols (IntelPairHmmCSource.cpp:29,61,89,103; pairhmm_common.cc:3)
     for name in phmm.LEGACY_EXPORTS:
         assert hasattr(lib, name), name
-    assert lib.phmm_abi_version() == 2
+    assert lib.phmm_abi_version() == 3
 
 
 def test_no_cpu_fallback_without_a_device():
@@ -114,6 +114,67 @@ def test_parser_matches_the_reference_driver_semantics():
     for bad in (b"1 1\nACGT !!! !!!! !!!! !!!!\nAC\n", b"1 1\nACGT !!!! !!!! !!!!\n", b"x 1\n", b"2 1\nA ! ! ! !\nAC\n"):
         with pytest.raises(phmm.PhmmError) as e:
             phmm.parse_text(bad)
+        assert e.value.code == 6
+
+
+def test_binary_cache_round_trip_and_corruption(tmp_path):
+    fb = synth.generic(11, 9, (1, 12), (1, 6), (1, 200), (1, 300), q_rng=(6, 45), foreign_frac=0.2)
+    path = str(tmp_path / "b.phmmsoa")
+    phmm.cache_write(fb, path)
+    a = phmm.cache_open(path)
+    for k in ("batch_num_reads", "batch_num_haps", "read_len", "read_off", "hap_len", "hap_off",
+              "rs", "q", "i", "d", "c", "hap"):
+        assert np.array_equal(getattr(a, k), getattr(fb, k)), k
+    # a shard that points into larger pools is stored packed
+    shard = fb.select_batches(np.arange(1, fb.n_batches, 3))
+    phmm.cache_write(shard, path)
+    b = phmm.cache_open(path)
+    assert len(b.rs) == int(shard.read_len.sum()) and len(b.hap) == int(shard.hap_len.sum())
+    ra, rb = oracle.run_port(shard), oracle.run_port(b)
+    assert np.array_equal(ra.out.view(np.uint64), rb.out.view(np.uint64))
+    # empty set of batches
+    phmm.cache_write(fb.select_batches(np.arange(0)), path)
+    assert phmm.cache_open(path).n_batches == 0
+    # corruption, truncation and foreign files are refused, not read
+    phmm.cache_write(fb, path)
+    raw = bytearray(open(path, "rb").read())
+    for pos in (3, 60, 130, len(raw) - 5):
+        bad = bytearray(raw)
+        bad[pos] ^= 0x40
+        open(path, "wb").write(bad)
+        with pytest.raises(phmm.PhmmError) as e:
+            phmm.cache_open(path)
+        assert e.value.code == 6, pos
+    open(path, "wb").write(raw[:len(raw) // 2])
+    with pytest.raises(phmm.PhmmError):
+        phmm.cache_open(path)
+    with pytest.raises(phmm.PhmmError) as e:
+        phmm.cache_open(str(tmp_path / "missing"))
+    assert e.value.code == 7
+
+
+def test_gatk_testdata_loader():
+    # the line format of GATK's pairhmm-testdata.txt as dataFileTest reads it
+    # (PairHmmUnitTest.java:166-185); the file itself is not in the reference checkout, so the
+    # vectors here are the reference's own simpleTest (:42-55) and SURVEY.md 8c's tiny.in pairs
+    txt = (b"# hap read quals ins del gcp expected\n"
+           b"ACGT ACGT LLLL LLLL LLLL LLLL -6.022797e-01\n"
+           b"#comment line\n"
+           b"  TTACGTACGTACTT\tACGTACGTAC IIIIIIIIII NNNNNNNNNN NNNNNNNNNN ++++++++++ -1.192551\n"
+           b"ACGT ACGT !!+5 !!!+ \"#$% ++++ 0\n")
+    fb, exp = phmm.parse_testdata(txt)
+    assert fb.n_batches == 3 and fb.n_pairs == 3 and exp.tolist() == [-6.022797e-01, -1.192551, 0.0]
+    assert fb.hap.tobytes() == b"ACGTTTACGTACGTACTTACGT" and fb.read_len.tolist() == [4, 10, 4]
+    # normalize(): byte - 33, read quals floored at 6 (:268-278)
+    assert fb.q[:4].tolist() == [43] * 4 and fb.q[-4:].tolist() == [6, 6, 10, 20]
+    assert fb.i[-4:].tolist() == [0, 0, 0, 10] and fb.d[-4:].tolist() == [1, 2, 3, 4]
+    r = oracle.run_port(fb)
+    assert abs(r.out[0] - exp[0]) < 1e-5 and abs(r.out[1] - exp[1]) < 1e-5     # the test's own bar
+    assert phmm.parse_testdata(b"# only a comment\n")[0].n_batches == 0
+    for bad in (b"ACGT ACGT LLLL LLLL LLLL LLLL\n", b"ACGT ACGT LLL LLLL LLLL LLLL -1\n",
+                b"ACGT ACGT LLLL LLLL LLLL LLLL x\n"):
+        with pytest.raises(phmm.PhmmError) as e:
+            phmm.parse_testdata(bad)
         assert e.value.code == 6
 
 
