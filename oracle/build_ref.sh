@@ -16,6 +16,8 @@ mkdir -p "$OUT"
 gcc -O2 -std=c11 -fPIC -shared -fopenmp -ffp-contract=off \
     -o "$OUT/liboracle.so" "$HERE/phmm_oracle.c" -lm
 echo "built $OUT/liboracle.so"
+gcc -O2 -std=c11 -fPIC -shared -fopenmp -o "$OUT/libsw_oracle.so" "$HERE/sw_oracle.c"
+echo "built $OUT/libsw_oracle.so"
 
 if [ ! -d "$P/pairhmm" ]; then
   echo "reference sources not found at $P -- keeping any prebuilt $OUT/libphmm_ref.so"
@@ -49,3 +51,14 @@ build_variant () {   # $1 = output name, $2 = extra flags
 }
 build_variant libphmm_ref.so "-ffp-contract=off"
 build_variant libphmm_ref_fma.so ""
+
+# ---- Smith-Waterman: avx2_impl.cc / avx512_impl.cc include PairWiseSW.h ----
+S="$P/smithwaterman"
+obj="$OUT/obj_sw"; mkdir -p "$obj"
+SWF="-O2 -std=c++11 -fPIC -fopenmp -w -I$P/common -I$S"
+g++ $SWF -mavx -mavx2 -c "$S/avx2_impl.cc" -o "$obj/avx2_impl.o"
+g++ $SWF -mavx -mavx2 -mavx512f -mavx512dq -mavx512vl -mavx512bw -c "$S/avx512_impl.cc" -o "$obj/avx512_impl.o"
+g++ $SWF -c "$HERE/sw_ref_harness.cpp" -o "$obj/sw_ref_harness.o"
+g++ -shared -fopenmp -Wl,-Bsymbolic -o "$OUT/libsw_ref.so" "$obj"/*.o
+rm -rf "$obj"
+echo "built $OUT/libsw_ref.so"
