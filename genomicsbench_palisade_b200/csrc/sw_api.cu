@@ -1,0 +1,405 @@
+// C ABI of libsw_cuda: context, device-resident workloads, host-buffer entry points and the
+// reference's own C entry points.  Contract and reference interfaces: include/sw_cuda.h.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/sw_cuda.h"
+#include "sw_kernels.cuh"
+
+using namespace sw;
+
+namespace {
+thread_local std::string g_create_error;
+const int N_CLASSES = 4;                       // KH = 1, 2, 4, 8 rows per lane
+const int CLASS_KH[N_CLASSES] = {1, 2, 4, 8};
+
+typedef void (*Kernel)(const Params);
+Kernel kernel_for(int c)
+{
+    switch (c) {
+    case 0: return sw_align_kernel<1>;
+    case 1: return sw_align_kernel<2>;
+    case 2: return sw_align_kernel<4>;
+    default: return sw_align_kernel<8>;
+    }
+}
+}  // namespace
+
+struct sw_ctx {
+    int device = 0, sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    int blocks_per_sm[N_CLASSES] = {0, 0, 0, 0};
+    std::string error;
+    std::mutex mu;
+};
+
+struct sw_workload {
+    sw_ctx *ctx = nullptr;
+    int64_t n_pairs = 0, n_cells = 0, h2d_bytes = 0, bt_bytes = 0;
+    int32_t cigar_stride = 0;
+    int32_t class_ntasks[N_CLASSES] = {0, 0, 0, 0};
+    int64_t class_off[N_CLASSES] = {0, 0, 0, 0};
+    int64_t class_bt_stride[N_CLASSES] = {0, 0, 0, 0};
+    int class_grid[N_CLASSES] = {0, 0, 0, 0};
+    int32_t elems_stride = 0;
+    uint8_t *d_base = nullptr;           // one allocation
+    uint8_t *d_ref = nullptr, *d_alt = nullptr;
+    PairRec *d_pairs = nullptr;
+    int32_t *d_score = nullptr, *d_offset = nullptr, *d_cigar_len = nullptr, *d_counters = nullptr;
+    char *d_cigar = nullptr;
+    uint32_t *d_bt = nullptr;
+    int2 *d_elems = nullptr;
+    int launches = 0;
+};
+
+#define SW_TRY(ctx, expr)                                                                      \
+    do {                                                                                       \
+        cudaError_t e__ = (expr);                                                              \
+        if (e__ != cudaSuccess) {                                                              \
+            (ctx)->error = std::string(#expr) + ": " + cudaGetErrorString(e__);                \
+            return SW_ERR_CUDA;                                                                \
+        }                                                                                      \
+    } while (0)
+
+extern "C" int sw_abi_version(void) { return SW_ABI_VERSION; }
+
+extern "C" const char *sw_last_error(const sw_ctx *ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+extern "C" int sw_create(int device, sw_ctx **out)
+{
+    if (!out) return SW_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        g_create_error = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                         " (libsw_cuda has no CPU fallback)";
+        return SW_ERR_CUDA;
+    }
+    if (device < 0 || device >= n) { g_create_error = "device index out of range"; return SW_ERR_ARG; }
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return SW_ERR_CUDA; }
+    if (prop.major != 10) {
+        char buf[160];
+        snprintf(buf, sizeof buf, "device %d is sm_%d%d; libsw_cuda is built for sm_100a (B200) only", device, prop.major, prop.minor);
+        g_create_error = buf;
+        return SW_ERR_CUDA;
+    }
+    sw_ctx *ctx = new sw_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    auto bail = [&](const char *what, cudaError_t err) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
+        sw_destroy(ctx);
+        return SW_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    for (int k = 0; k < 2; ++k)
+        if ((e = cudaEventCreate(&ctx->ev[k])) != cudaSuccess) return bail("cudaEventCreate", e);
+    const int smem = WARPS_PER_BLOCK * (int)sizeof(WarpSmem);
+    for (int c = 0; c < N_CLASSES; ++c) {
+        Kernel k = kernel_for(c);
+        if ((e = cudaFuncSetAttribute((const void *)k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess)
+            return bail("cudaFuncSetAttribute", e);
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void *)k, WARPS_PER_BLOCK * 32, smem) != cudaSuccess || nb < 1) nb = 1;
+        ctx->blocks_per_sm[c] = nb;
+    }
+    *out = ctx;
+    return SW_OK;
+}
+
+extern "C" int sw_destroy(sw_ctx *ctx)
+{
+    if (!ctx) return SW_OK;
+    cudaSetDevice(ctx->device);
+    for (int k = 0; k < 2; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return SW_OK;
+}
+
+extern "C" int sw_workload_destroy(sw_workload *w)
+{
+    if (!w) return SW_OK;
+    if (w->ctx) { cudaSetDevice(w->ctx->device); cudaFree(w->d_base); }
+    delete w;
+    return SW_OK;
+}
+
+static int check_params(sw_ctx *ctx, const sw_params *pm, int strategy)
+{
+    if (!pm) { ctx->error = "NULL parameters"; return SW_ERR_ARG; }
+    if (strategy < SW_SOFTCLIP || strategy > SW_IGNORE) { ctx->error = "unknown overhang strategy (expected 9..12)"; return SW_ERR_ARG; }
+    const int32_t v[4] = {pm->match, pm->mismatch, pm->open, pm->extend};
+    for (int k = 0; k < 4; ++k)
+        if (v[k] > SW_MAX_ABS_PARAM || v[k] < -SW_MAX_ABS_PARAM) { ctx->error = "scoring parameter out of range"; return SW_ERR_ARG; }
+    return SW_OK;
+}
+
+extern "C" int sw_workload_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, sw_workload **out)
+{
+    if (!ctx || !fp || !out) return SW_ERR_ARG;
+    *out = nullptr;
+    const int64_t n = fp->n_pairs;
+    if (n < 0 || n > INT32_MAX || cigar_stride < 2) { ctx->error = "bad pair count or cigar stride"; return SW_ERR_ARG; }
+    if (n && (!fp->ref_len || !fp->ref_off || !fp->ref_pool || !fp->alt_len || !fp->alt_off || !fp->alt_pool)) {
+        ctx->error = "NULL array in sw_flat_pairs";
+        return SW_ERR_ARG;
+    }
+    // validate; the referenced range of each pool is uploaded as one piece
+    int64_t rlo = INT64_MAX, rhi = 0, alo = INT64_MAX, ahi = 0, cells = 0;
+    for (int64_t p = 0; p < n; ++p) {
+        const int32_t l1 = fp->ref_len[p], l2 = fp->alt_len[p];
+        if (l1 <= 0 || l2 <= 0) { ctx->error = "sequence of length <= 0"; return SW_ERR_EMPTY_SEQ; }
+        if (l1 > SW_MAX_SEQ_LEN || l2 > SW_MAX_SEQ_LEN) { ctx->error = "sequence longer than SW_MAX_SEQ_LEN"; return SW_ERR_TOO_LONG; }
+        if (fp->ref_off[p] < 0 || fp->alt_off[p] < 0) { ctx->error = "negative pool offset"; return SW_ERR_ARG; }
+        rlo = std::min(rlo, fp->ref_off[p]); rhi = std::max(rhi, fp->ref_off[p] + l1);
+        alo = std::min(alo, fp->alt_off[p]); ahi = std::max(ahi, fp->alt_off[p] + l2);
+        cells += (int64_t)l1 * l2;
+    }
+    if (n == 0) { rlo = rhi = alo = ahi = 0; }
+    sw_workload *w = new sw_workload();
+    w->ctx = ctx;
+    w->n_pairs = n;
+    w->n_cells = cells;
+    w->cigar_stride = cigar_stride;
+
+    // ---- classes by rows per lane, tasks longest first ----------------------------------------------
+    std::vector<PairRec> recs[N_CLASSES];
+    int max_sum = 0;
+    for (int64_t p = 0; p < n; ++p) {
+        const int32_t l1 = fp->ref_len[p], l2 = fp->alt_len[p];
+        int c = 0;
+        while (c < N_CLASSES - 1 && 32 * CLASS_KH[c] < l1) ++c;
+        PairRec r;
+        r.ref_off = fp->ref_off[p] - rlo; r.alt_off = fp->alt_off[p] - alo;
+        r.ref_len = l1; r.alt_len = l2; r.out = (int32_t)p; r.pad = 0;
+        recs[c].push_back(r);
+        max_sum = std::max(max_sum, l1 + l2);
+        const int kh = CLASS_KH[c], stripes = (l1 + 32 * kh - 1) / (32 * kh);
+        w->class_bt_stride[c] = std::max<int64_t>(w->class_bt_stride[c], (int64_t)stripes * (l2 + 31) * 32);
+        w->bt_bytes += (int64_t)stripes * (l2 + std::min(32, (l1 + kh - 1) / kh) - 1) * 128;
+    }
+    w->elems_stride = max_sum + 8;
+    std::vector<PairRec> all;
+    all.reserve((size_t)n);
+    int64_t bt_words = 1, warps_max = 1;
+    for (int c = 0; c < N_CLASSES; ++c) {
+        std::stable_sort(recs[c].begin(), recs[c].end(), [](const PairRec &a, const PairRec &b) {
+            return (int64_t)a.ref_len * a.alt_len > (int64_t)b.ref_len * b.alt_len;
+        });
+        w->class_off[c] = (int64_t)all.size();
+        w->class_ntasks[c] = (int32_t)recs[c].size();
+        all.insert(all.end(), recs[c].begin(), recs[c].end());
+        const int64_t full = (int64_t)ctx->blocks_per_sm[c] * ctx->sm_count;
+        const int64_t want = ((int64_t)recs[c].size() + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
+        w->class_grid[c] = (int)std::max<int64_t>(1, std::min(full, want));
+        const int64_t warps = (int64_t)w->class_grid[c] * WARPS_PER_BLOCK;
+        bt_words = std::max(bt_words, warps * w->class_bt_stride[c]);
+        warps_max = std::max(warps_max, warps);
+    }
+
+    auto fail = [&](int code) { sw_workload_destroy(w); return code; };
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->error = "cudaSetDevice failed"; return fail(SW_ERR_CUDA); }
+    const size_t np = (size_t)std::max<int64_t>(1, n);
+    struct Piece { void **ptr; size_t bytes; };
+    const Piece pieces[] = {
+        {(void **)&w->d_ref, (size_t)(rhi - rlo)}, {(void **)&w->d_alt, (size_t)(ahi - alo)},
+        {(void **)&w->d_pairs, np * sizeof(PairRec)},
+        {(void **)&w->d_score, np * 4}, {(void **)&w->d_offset, np * 4}, {(void **)&w->d_cigar_len, np * 4},
+        {(void **)&w->d_counters, 64 * 4},
+        {(void **)&w->d_cigar, np * (size_t)cigar_stride},
+        {(void **)&w->d_bt, (size_t)bt_words * 4},
+        {(void **)&w->d_elems, (size_t)(warps_max * w->elems_stride) * sizeof(int2)},
+    };
+    size_t total = 0;
+    for (const Piece &p : pieces) total += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255;
+    cudaError_t e = cudaMalloc((void **)&w->d_base, total);
+    if (e != cudaSuccess) {
+        ctx->error = std::string("cudaMalloc: ") + cudaGetErrorString(e);
+        return fail(e == cudaErrorMemoryAllocation ? SW_ERR_NOMEM : SW_ERR_CUDA);
+    }
+    size_t off = 0;
+    for (const Piece &p : pieces) { *p.ptr = w->d_base + off; off += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255; }
+    cudaStream_t st = ctx->stream;
+    if (n) {
+        if ((e = cudaMemcpyAsync(w->d_ref, fp->ref_pool + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
+            (e = cudaMemcpyAsync(w->d_alt, fp->alt_pool + alo, (size_t)(ahi - alo), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
+            (e = cudaMemcpyAsync(w->d_pairs, all.data(), all.size() * sizeof(PairRec), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
+            (e = cudaStreamSynchronize(st)) != cudaSuccess) {
+            ctx->error = std::string("upload: ") + cudaGetErrorString(e);
+            return fail(SW_ERR_CUDA);
+        }
+    }
+    w->h2d_bytes = (rhi - rlo) + (ahi - alo) + (int64_t)all.size() * (int64_t)sizeof(PairRec);
+    *out = w;
+    return SW_OK;
+}
+
+static int wl_launch(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strategy)
+{
+    cudaStream_t st = ctx->stream;
+    SW_TRY(ctx, cudaSetDevice(ctx->device));
+    SW_TRY(ctx, cudaMemsetAsync(w->d_counters, 0, 64 * 4, st));
+    SW_TRY(ctx, cudaEventRecord(ctx->ev[0], st));
+    w->launches = 0;
+    // longest-running class first: its tail is covered by the blocks of the next
+    for (int c = N_CLASSES - 1; c >= 0; --c) {
+        if (w->class_ntasks[c] == 0) continue;
+        Params P;
+        memset(&P, 0, sizeof P);
+        P.ref_pool = w->d_ref; P.alt_pool = w->d_alt;
+        P.pairs = w->d_pairs + w->class_off[c];
+        P.ntasks = w->class_ntasks[c];
+        P.counter = w->d_counters + c;
+        P.match = pm->match; P.mismatch = pm->mismatch; P.open = pm->open; P.extend = pm->extend;
+        P.strategy = strategy;
+        P.bt = w->d_bt; P.bt_stride = w->class_bt_stride[c];
+        P.elems = w->d_elems; P.elems_stride = w->elems_stride;
+        P.score = w->d_score; P.offset = w->d_offset; P.cigar_len = w->d_cigar_len;
+        P.cigar = w->d_cigar; P.cigar_stride = w->cigar_stride;
+        kernel_for(c)<<<w->class_grid[c], WARPS_PER_BLOCK * 32, WARPS_PER_BLOCK * sizeof(WarpSmem), st>>>(P);
+        SW_TRY(ctx, cudaGetLastError());
+        ++w->launches;
+    }
+    SW_TRY(ctx, cudaEventRecord(ctx->ev[1], st));
+    return SW_OK;
+}
+
+static void fill_stats(sw_ctx *ctx, sw_workload *w, sw_stats *stats)
+{
+    if (!stats) return;
+    memset(stats, 0, sizeof *stats);
+    stats->n_pairs = w->n_pairs;
+    stats->n_cells = w->n_cells;
+    stats->h2d_bytes = w->h2d_bytes;
+    stats->bt_bytes = w->bt_bytes;
+    stats->n_launches = w->launches;
+    for (int c = 0; c < N_CLASSES; ++c) stats->n_classes += w->class_ntasks[c] > 0;
+    float ms = 0.0f;
+    if (w->launches && cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) stats->ms_kernels = ms;
+}
+
+extern "C" int sw_workload_run(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strategy, sw_stats *stats)
+{
+    if (!ctx || !w || w->ctx != ctx) return SW_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = check_params(ctx, pm, strategy);
+    if (rc != SW_OK) return rc;
+    rc = wl_launch(ctx, w, pm, strategy);
+    if (rc != SW_OK) return rc;
+    SW_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    fill_stats(ctx, w, stats);
+    return SW_OK;
+}
+
+extern "C" int sw_workload_results(sw_ctx *ctx, sw_workload *w, int32_t *score, int32_t *offset, char *cigar,
+                                   int32_t *cigar_len)
+{
+    if (!ctx || !w || w->ctx != ctx) return SW_ERR_ARG;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    SW_TRY(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)w->n_pairs;
+    if (n == 0) return SW_OK;
+    cudaStream_t st = ctx->stream;
+    if (score) SW_TRY(ctx, cudaMemcpyAsync(score, w->d_score, n * 4, cudaMemcpyDeviceToHost, st));
+    if (offset) SW_TRY(ctx, cudaMemcpyAsync(offset, w->d_offset, n * 4, cudaMemcpyDeviceToHost, st));
+    if (cigar_len) SW_TRY(ctx, cudaMemcpyAsync(cigar_len, w->d_cigar_len, n * 4, cudaMemcpyDeviceToHost, st));
+    if (cigar) SW_TRY(ctx, cudaMemcpyAsync(cigar, w->d_cigar, n * (size_t)w->cigar_stride, cudaMemcpyDeviceToHost, st));
+    SW_TRY(ctx, cudaStreamSynchronize(st));
+    return SW_OK;
+}
+
+extern "C" int sw_align_flat(sw_ctx *ctx, const sw_flat_pairs *fp, const sw_params *pm, int strategy, int32_t *score,
+                             int32_t *offset, char *cigar, int32_t cigar_stride, int32_t *cigar_len, sw_stats *stats)
+{
+    if (!ctx || !fp) return SW_ERR_ARG;
+    int rc = check_params(ctx, pm, strategy);
+    if (rc != SW_OK) return rc;
+    if (fp->n_pairs && (!cigar || !cigar_len)) { ctx->error = "NULL cigar output"; return SW_ERR_ARG; }
+    struct timespec t0, t1;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    sw_workload *w = nullptr;
+    rc = sw_workload_create(ctx, fp, cigar_stride, &w);
+    if (rc != SW_OK) return rc;
+    sw_stats st;
+    rc = sw_workload_run(ctx, w, pm, strategy, &st);
+    if (rc == SW_OK) rc = sw_workload_results(ctx, w, score, offset, cigar, cigar_len);
+    sw_workload_destroy(w);
+    if (rc != SW_OK) return rc;
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    for (int64_t p = 0; p < fp->n_pairs; ++p) st.n_overflow += cigar_len[p] < 0;
+    st.d2h_bytes = fp->n_pairs * (12 + (int64_t)cigar_stride);
+    st.ms_total = (float)((t1.tv_sec - t0.tv_sec) * 1e3 + (t1.tv_nsec - t0.tv_nsec) * 1e-6);
+    if (stats) *stats = st;
+    return SW_OK;
+}
+
+extern "C" int sw_align_one(sw_ctx *ctx, const uint8_t *ref, int32_t ref_len, const uint8_t *alt, int32_t alt_len,
+                            const sw_params *pm, int strategy, char *cigar, int32_t cigar_cap, int32_t *score,
+                            int32_t *offset)
+{
+    if (!ctx || !ref || !alt || !cigar) return SW_ERR_ARG;
+    const int64_t zero = 0;
+    sw_flat_pairs fp;
+    fp.n_pairs = 1;
+    fp.ref_len = &ref_len; fp.ref_off = &zero; fp.ref_pool = ref;
+    fp.alt_len = &alt_len; fp.alt_off = &zero; fp.alt_pool = alt;
+    // device slot sized for the longest possible string (one element per traceback step); only
+    // the string itself is copied into the caller's buffer
+    const int32_t stride = 5 * (ref_len + alt_len) + 16;
+    std::vector<char> tmp((size_t)std::max(stride, 16));
+    int32_t len = 0;
+    int rc = sw_align_flat(ctx, &fp, pm, strategy, score, offset, tmp.data(), stride, &len, nullptr);
+    if (rc != SW_OK) return rc;
+    if (len < 0 || len + 1 > cigar_cap) { ctx->error = "CIGAR does not fit cigar_cap"; return SW_ERR_ARG; }
+    memcpy(cigar, tmp.data(), (size_t)len + 1);
+    return SW_OK;
+}
+
+// ============================================================================================
+// the reference's C entry points (IntelSmithWatermanCSource.cpp:22-57)
+// ============================================================================================
+namespace {
+sw_ctx *g_legacy = nullptr;
+std::mutex g_legacy_mu;
+}
+
+extern "C" void initNative(void)
+{
+    std::lock_guard<std::mutex> lk(g_legacy_mu);
+    if (g_legacy) return;
+    const char *d = getenv("SW_DEVICE");
+    if (sw_create(d ? atoi(d) : 0, &g_legacy) != SW_OK) {
+        fprintf(stderr, "libsw_cuda: initNative: %s\n", sw_last_error(nullptr));
+        abort();
+    }
+}
+
+extern "C" void align(char *ref, char *alt, char *cigar, int match, int mismatch, int open, int extend, int strategy,
+                      int *score, int *offset)
+{
+    if (!g_legacy) initNative();
+    const sw_params pm = {match, mismatch, open, extend};
+    const int l1 = (int)strlen(ref), l2 = (int)strlen(alt);
+    int32_t sc = 0, off = 0;
+    // the reference sprintf()s into `cigar` without a bound: exactly strlen + 1 bytes are written here too
+    const int rc = sw_align_one(g_legacy, (const uint8_t *)ref, l1, (const uint8_t *)alt, l2, &pm, strategy, cigar,
+                                INT32_MAX, &sc, &off);
+    if (rc != SW_OK) {
+        fprintf(stderr, "libsw_cuda: align: %s\n", sw_last_error(g_legacy));
+        abort();
+    }
+    if (score) *score = sc;
+    if (offset) *offset = off;
+}

@@ -1,0 +1,274 @@
+// Smith-Waterman with backtrack for sm_100a: one warp per (ref, alt) pair.
+//
+// Computes what smithWatermanBackTrack + getCIGAR compute
+// (tools/GKL/src/main/native/smithwaterman/PairWiseSW.h:40-263, :265-412), bit for bit:
+//
+//   * Wavefront over a stripe of 32 * KH rows: lane l owns rows base + l*KH .. + KH-1 in registers
+//     (H and E of the previous column), works on column step - l, and hands the H and F of its bottom
+//     row to lane l + 1 with __shfl_up_sync.  The reference sweeps anti-diagonals with 8/16-wide
+//     vectors through three memory arrays (:98-194); here the diagonal state never leaves registers.
+//   * ref longer than one stripe: the bottom row of a stripe (H, F per column) stays in shared
+//     memory for the next stripe.
+//   * Backtrack: 4 bits per cell (MATCH/INSERT/DELETE + the two *_EXT flags, :21-25), the KH cells a
+//     lane computes in one step packed into one 32-bit word, stored at [stripe][step][lane] -- one
+//     coalesced 128-byte line per warp and step.  The reference writes 16 bits per cell (:170).
+//   * Last row / last column scores go to shared memory; the best cell is chosen afterwards in the
+//     reference's visiting order (:209-236): a warp-wide maximum, then the tie rule applied to the
+//     cells that reach it, in anti-diagonal order.
+//   * Traceback and CIGAR formatting (:265-412) by the warp on the backtrack words it just wrote.
+#ifndef SW_KERNELS_CUH
+#define SW_KERNELS_CUH
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace sw {
+
+static const int WARPS_PER_BLOCK = 4;
+static const int MAX_LEN = 1024;
+static const unsigned FULL = 0xffffffffu;
+
+enum { OP_MATCH = 0, OP_INSERT = 1, OP_DELETE = 2, F_INSERT_EXT = 4, F_DELETE_EXT = 8,
+       ST_SOFTCLIP = 9, ST_INDEL = 10, ST_LEADING_INDEL = 11, ST_IGNORE = 12 };
+#define SW_MIN_CUTOFF (-100000000)              /* MATRIX_MIN_CUTOFF, smithwaterman_common.h:52 */
+#define SW_LOW_INIT   (INT32_MIN / 2)           /* LOW_INIT_VALUE, :53 */
+
+struct PairRec {            // 32 bytes
+    int64_t ref_off, alt_off;   // into the device pools
+    int32_t ref_len, alt_len;
+    int32_t out;                // result index (the caller's pair number)
+    int32_t pad;
+};
+
+struct Params {
+    const uint8_t *ref_pool, *alt_pool;
+    const PairRec *pairs;       // this class's tasks, longest first
+    int32_t ntasks;
+    int32_t *counter;           // queue head
+    int32_t match, mismatch, open, extend, strategy;
+    uint32_t *bt;               // per-warp backtrack scratch
+    int64_t bt_stride;          // words per warp
+    int2 *elems;                // per-warp CIGAR element scratch
+    int32_t elems_stride;
+    int32_t *score, *offset, *cigar_len;
+    char *cigar;
+    int32_t cigar_stride;
+};
+
+// per-warp shared memory: stripe boundary H / F, last row, last column, alt bytes
+struct __align__(16) WarpSmem {
+    int32_t hb[MAX_LEN + 1], fb[MAX_LEN + 1];
+    int32_t lastrow[MAX_LEN + 1], lastcol[MAX_LEN + 1];
+    uint8_t alt[MAX_LEN + 16];
+};
+
+__device__ __forceinline__ int iabs(int x) { return x < 0 ? -x : x; }
+
+template <int KH>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+sw_align_kernel(const Params P)
+{
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    WarpSmem &S = reinterpret_cast<WarpSmem *>(smem_raw)[threadIdx.x >> 5];
+    const int lane = threadIdx.x & 31;
+    const int warp_global = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+    uint32_t *bt = P.bt + (int64_t)warp_global * P.bt_stride;
+    int2 *elems = P.elems + (int64_t)warp_global * P.elems_stride;
+    constexpr int STRIPE = 32 * KH;
+    const bool lead = (P.strategy == ST_INDEL || P.strategy == ST_LEADING_INDEL);
+
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(P.counter, 1);
+        t = __shfl_sync(FULL, t, 0);
+        if (t >= P.ntasks) break;
+        const PairRec pr = P.pairs[t];
+        const int nrow = pr.ref_len, ncol = pr.alt_len;
+        const uint8_t *seq1 = P.ref_pool + pr.ref_off;
+        __syncwarp();
+        for (int k = lane; k < ncol; k += 32) S.alt[k] = P.alt_pool[pr.alt_off + k];
+        __syncwarp();
+
+        const int nstripes = (nrow + STRIPE - 1) / STRIPE;
+        const int T = ncol + 31;                         // steps per stripe (stride of the backtrack words)
+        for (int s = 0; s < nstripes; ++s) {
+            const int base = s * STRIPE;                 // rows base + 1 .. base + STRIPE
+            const int i0 = base + lane * KH + 1;         // first row of this lane (1-based)
+            const int rows_here = min(STRIPE, nrow - base);
+            const int lanes_used = (rows_here + KH - 1) / KH;
+            const bool last_stripe = (s == nstripes - 1);
+            // column-0 boundary (:196-205): H(i, 0) = open + (i - 1) * extend or 0; E(i, 0) = LOW (:207)
+            int32_t Hl[KH], E[KH];
+            uint32_t c1[KH];
+#pragma unroll
+            for (int p = 0; p < KH; ++p) {
+                const int i = i0 + p;
+                Hl[p] = lead ? P.open + (i - 1) * P.extend : 0;
+                E[p] = SW_LOW_INIT;
+                c1[p] = (i <= nrow) ? (uint32_t)seq1[i - 1] : 0x100u;    // padding rows match nothing
+            }
+            // H(i0 - 1, 0): diagonal neighbour of the lane's first row at column 1
+            int32_t Hd_next = (i0 - 1 == 0) ? 0 : (lead ? P.open + (i0 - 2) * P.extend : 0);
+            int32_t Hbot = 0, Fbot = SW_LOW_INIT;
+            const int pr_row = (nrow - 1) % KH;          // register slot of row nrow in its lane
+            const int lr_lane = ((nrow - 1) % STRIPE) / KH;
+            const int steps = ncol + lanes_used - 1;
+            for (int st = 0; st < steps; ++st) {
+                const int j = st - lane + 1;             // this lane's column (1-based)
+                int32_t Ht = __shfl_up_sync(FULL, Hbot, 1);
+                int32_t Ft = __shfl_up_sync(FULL, Fbot, 1);
+                if (lane == 0) {
+                    const int jj = min(max(j, 0), ncol);
+                    if (s == 0) { Ht = lead ? P.open + (jj - 1) * P.extend : 0; Ft = SW_LOW_INIT; }   // row 0 (:196-206)
+                    else        { Ht = S.hb[jj]; Ft = S.fb[jj]; }
+                }
+                if (j >= 1 && j <= ncol && lane < lanes_used) {
+                    const uint32_t c2 = S.alt[j - 1];
+                    int32_t Hd = Hd_next;
+                    Hd_next = Ht;
+                    uint32_t word = 0;
+                    int32_t hsel = 0;
+#pragma unroll
+                    for (int p = 0; p < KH; ++p) {
+                        // MAIN_CODE (:3-37)
+                        const int32_t open_h = Hl[p] + P.open, ext_h = E[p] + P.extend;
+                        const int32_t e11 = max(open_h, ext_h);
+                        uint32_t b = (open_h > ext_h) ? 0u : (uint32_t)F_INSERT_EXT;
+                        const int32_t open_v = Ht + P.open, ext_v = Ft + P.extend;
+                        const int32_t f11 = max(ext_v, open_v);
+                        b |= (open_v > ext_v) ? 0u : (uint32_t)F_DELETE_EXT;
+                        const int32_t m11 = Hd + ((c1[p] == c2) ? P.match : P.mismatch);
+                        int32_t h11 = max(m11, SW_MIN_CUTOFF);
+                        b |= (e11 > h11) ? (uint32_t)OP_INSERT : 0u;
+                        h11 = max(h11, e11);
+                        if (f11 > h11) b = (b & ~3u) | (uint32_t)OP_DELETE;
+                        h11 = max(h11, f11);
+                        word |= b << (4 * p);
+                        Hd = Hl[p];
+                        Ht = h11; Ft = f11;
+                        Hl[p] = h11; E[p] = e11;
+                        if (p == pr_row) hsel = h11;
+                    }
+                    Hbot = Ht; Fbot = Ft;
+                    bt[((int64_t)s * T + st) * 32 + lane] = word;
+                    if (!last_stripe && lane == 31) { S.hb[j] = Hbot; S.fb[j] = Fbot; }
+                    if (last_stripe && lane == lr_lane) S.lastrow[j] = hsel;
+                    if (j == ncol) {
+#pragma unroll
+                        for (int p = 0; p < KH; ++p)
+                            if (i0 + p <= nrow) S.lastcol[i0 + p] = Hl[p];
+                    }
+                }
+            }
+            __syncwarp();
+            if (!last_stripe && lane == 0) {             // H(base + STRIPE, 0) for the next stripe's lane 0
+                S.hb[0] = lead ? P.open + (base + STRIPE - 1) * P.extend : 0;
+                S.fb[0] = SW_LOW_INIT;
+            }
+            __syncwarp();
+        }
+
+        // ---- best last-row / last-column cell in the reference's visiting order (:209-236) ----------
+        // slot 2d = (nrow, d - nrow) for d >= nrow + 1 (SOFTCLIP / IGNORE only), slot 2d + 1 = (d - ncol, ncol)
+        // for d >= ncol + 1, d = 1 .. nrow + ncol
+        const bool row_cands = (P.strategy == ST_SOFTCLIP || P.strategy == ST_IGNORE);
+        const int slot_lo = 2 * (min(nrow, ncol) + 1), slot_hi = 2 * (nrow + ncol) + 2;
+        auto slot_score = [&](int slot, int32_t *sc) -> bool {
+            const int d = slot >> 1;
+            if (slot >= slot_hi) return false;
+            if (slot & 1) { if (d < ncol + 1) return false; *sc = S.lastcol[d - ncol]; return true; }
+            if (!row_cands || d < nrow + 1) return false;
+            *sc = S.lastrow[d - nrow];
+            return true;
+        };
+        int32_t best = INT32_MIN;
+        for (int sl = slot_lo + lane; sl < slot_hi; sl += 32) {
+            int32_t sc;
+            if (slot_score(sl, &sc)) best = max(best, sc);
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) best = max(best, __shfl_xor_sync(FULL, best, o));
+        int max_i = 0, max_j = 0;
+        bool have = false;
+        for (int sl0 = slot_lo; sl0 < slot_hi; sl0 += 32) {
+            int32_t sc = 0;
+            const bool hit = slot_score(sl0 + lane, &sc) && sc == best;
+            unsigned m = __ballot_sync(FULL, hit);
+            while (m) {
+                const int sl = sl0 + __ffs(m) - 1;
+                m &= m - 1;
+                const int d = sl >> 1;
+                int ci, cj;
+                bool take;
+                if (sl & 1) { ci = d - ncol; cj = ncol; take = !have || max_j == ncol || iabs(ci - cj) <= iabs(max_i - max_j); }
+                else        { ci = nrow; cj = d - nrow; take = !have || iabs(ci - cj) < iabs(max_i - max_j); }
+                if (take) { max_i = ci; max_j = cj; have = true; }
+            }
+        }
+
+        // ---- traceback (getCIGAR :265-356), every lane in lock step on broadcast loads ---------------
+        int i, j, n = 0;
+        if (P.strategy == ST_INDEL) { i = nrow; j = ncol; }
+        else if (P.strategy == ST_LEADING_INDEL) { i = max_i; j = ncol; }
+        else { i = max_i; j = max_j; }
+        int cur_op = -1, cur_len = 0;                    // the element being built (equal neighbours merge, :372-388)
+        auto push = [&](int op, int len) {
+            if (op == cur_op) { cur_len += len; return; }
+            if (cur_op >= 0) { if (lane == 0) elems[n] = make_int2(cur_op, cur_len); ++n; }
+            cur_op = op; cur_len = len;
+        };
+        if (j < ncol) push(ST_SOFTCLIP, ncol - j);
+        int state = 0;
+        while (i > 0 && j > 0) {
+            const int r = (i - 1) % STRIPE, s = (i - 1) / STRIPE;
+            const int ln = r / KH, p = r % KH;
+            const uint32_t w = __ldcg(bt + ((int64_t)s * T + (j - 1 + ln)) * 32 + ln);
+            const int btr = (int)((w >> (4 * p)) & 15u);
+            if (state == F_INSERT_EXT) { --j; ++cur_len; state = btr & F_INSERT_EXT; }
+            else if (state == F_DELETE_EXT) { --i; ++cur_len; state = btr & F_DELETE_EXT; }
+            else {
+                const int op = btr & 3;
+                if (op == OP_MATCH) { --i; --j; push(OP_MATCH, 1); state = 0; }
+                else if (op == OP_INSERT) { --j; push(OP_INSERT, 1); state = btr & F_INSERT_EXT; }
+                else { --i; push(OP_DELETE, 1); state = btr & F_DELETE_EXT; }
+            }
+        }
+        int off;
+        if (P.strategy == ST_SOFTCLIP) { if (j > 0) push(ST_SOFTCLIP, j); off = i; }
+        else if (P.strategy == ST_IGNORE) { if (j > 0) push(cur_op, j); off = i - j; }     // repeats the last op (:363)
+        else { if (i > 0) push(OP_DELETE, i); else if (j > 0) push(OP_INSERT, j); off = 0; }
+        if (cur_op >= 0) { if (lane == 0) elems[n] = make_int2(cur_op, cur_len); ++n; }
+        __syncwarp();
+
+        // ---- CIGAR string, last element first (:390-410) -----------------------------------------------
+        if (lane == 0) {
+            int need = 0;
+            for (int k = 0; k < n; ++k) {
+                const int len = elems[k].y;
+                need += 1 + (len >= 1000 ? 4 : len >= 100 ? 3 : len >= 10 ? 2 : 1);
+            }
+            P.score[pr.out] = best;
+            P.offset[pr.out] = off;
+            if (need + 1 > P.cigar_stride) {
+                P.cigar_len[pr.out] = -1 - need;
+            } else {
+                char *out = P.cigar + (int64_t)pr.out * P.cigar_stride;
+                int at = 0;
+                for (int k = n - 1; k >= 0; --k) {
+                    const int2 e = elems[k];
+                    int len = e.y;
+                    const int nd = len >= 1000 ? 4 : len >= 100 ? 3 : len >= 10 ? 2 : 1;
+                    for (int q = nd - 1; q >= 0; --q) { out[at + q] = (char)('0' + len % 10); len /= 10; }
+                    at += nd;
+                    out[at++] = e.x == OP_MATCH ? 'M' : e.x == OP_INSERT ? 'I' : e.x == OP_DELETE ? 'D'
+                              : e.x == ST_SOFTCLIP ? 'S' : 'R';
+                }
+                out[at] = 0;
+                P.cigar_len[pr.out] = at;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace sw
+#endif
