@@ -17,8 +17,8 @@ using namespace sw;
 
 namespace {
 thread_local std::string g_create_error;
-const int N_CLASSES = 4;                       // KH = 1, 2, 4, 8 rows per lane
-const int CLASS_KH[N_CLASSES] = {1, 2, 4, 8};
+const int N_CLASSES = 12;                      // rows per lane; the last class covers SW_MAX_SEQ_LEN = 32 * 32
+const int CLASS_KH[N_CLASSES] = {1, 2, 3, 4, 6, 8, 10, 12, 16, 20, 24, 32};
 
 typedef void (*Kernel)(const Params);
 Kernel kernel_for(int c)
@@ -26,8 +26,16 @@ Kernel kernel_for(int c)
     switch (c) {
     case 0: return sw_align_kernel<1>;
     case 1: return sw_align_kernel<2>;
-    case 2: return sw_align_kernel<4>;
-    default: return sw_align_kernel<8>;
+    case 2: return sw_align_kernel<3>;
+    case 3: return sw_align_kernel<4>;
+    case 4: return sw_align_kernel<6>;
+    case 5: return sw_align_kernel<8>;
+    case 6: return sw_align_kernel<10>;
+    case 7: return sw_align_kernel<12>;
+    case 8: return sw_align_kernel<16>;
+    case 9: return sw_align_kernel<20>;
+    case 10: return sw_align_kernel<24>;
+    default: return sw_align_kernel<32>;
     }
 }
 }  // namespace
@@ -35,20 +43,26 @@ Kernel kernel_for(int c)
 struct sw_ctx {
     int device = 0, sm_count = 0;
     cudaStream_t stream = nullptr;
+    static const int N_SIDE = 4;            // class kernels run side by side: the tail of one is filled by the next
+    cudaStream_t side[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev[2] = {nullptr, nullptr};
-    int blocks_per_sm[N_CLASSES] = {0, 0, 0, 0};
+    uint8_t *arena = nullptr;               // grow-only device arena of the host-buffer entry points
+    size_t arena_cap = 0;
+    int blocks_per_sm[N_CLASSES] = {0};
     std::string error;
-    std::mutex mu;
+    std::recursive_mutex mu;           // sw_align_flat holds it across create / run / results (the arena is shared)
 };
 
 struct sw_workload {
     sw_ctx *ctx = nullptr;
     int64_t n_pairs = 0, n_cells = 0, h2d_bytes = 0, bt_bytes = 0;
     int32_t cigar_stride = 0;
-    int32_t class_ntasks[N_CLASSES] = {0, 0, 0, 0};
-    int64_t class_off[N_CLASSES] = {0, 0, 0, 0};
-    int64_t class_bt_stride[N_CLASSES] = {0, 0, 0, 0};
-    int class_grid[N_CLASSES] = {0, 0, 0, 0};
+    int32_t class_ntasks[N_CLASSES] = {0};
+    int64_t class_off[N_CLASSES] = {0};
+    int64_t class_bt_stride[N_CLASSES] = {0};
+    int class_grid[N_CLASSES] = {0};
+    int64_t class_bt_off[N_CLASSES] = {0}, class_elems_off[N_CLASSES] = {0};   // own scratch: classes run concurrently
     int32_t elems_stride = 0;
     uint8_t *d_base = nullptr;           // one allocation
     uint8_t *d_ref = nullptr, *d_alt = nullptr;
@@ -58,6 +72,7 @@ struct sw_workload {
     uint32_t *d_bt = nullptr;
     int2 *d_elems = nullptr;
     int launches = 0;
+    bool in_arena = false;               // buffers live in the context arena: nothing to free
 };
 
 #define SW_TRY(ctx, expr)                                                                      \
@@ -105,6 +120,11 @@ extern "C" int sw_create(int device, sw_ctx **out)
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     for (int k = 0; k < 2; ++k)
         if ((e = cudaEventCreate(&ctx->ev[k])) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    for (int k = 0; k < sw_ctx::N_SIDE; ++k) {
+        if ((e = cudaStreamCreateWithFlags(&ctx->side[k], cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+        if ((e = cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    }
     const int smem = WARPS_PER_BLOCK * (int)sizeof(WarpSmem);
     for (int c = 0; c < N_CLASSES; ++c) {
         Kernel k = kernel_for(c);
@@ -123,6 +143,12 @@ extern "C" int sw_destroy(sw_ctx *ctx)
     if (!ctx) return SW_OK;
     cudaSetDevice(ctx->device);
     for (int k = 0; k < 2; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    for (int k = 0; k < sw_ctx::N_SIDE; ++k) {
+        if (ctx->ev_join[k]) cudaEventDestroy(ctx->ev_join[k]);
+        if (ctx->side[k]) cudaStreamDestroy(ctx->side[k]);
+    }
+    cudaFree(ctx->arena);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return SW_OK;
@@ -131,7 +157,7 @@ extern "C" int sw_destroy(sw_ctx *ctx)
 extern "C" int sw_workload_destroy(sw_workload *w)
 {
     if (!w) return SW_OK;
-    if (w->ctx) { cudaSetDevice(w->ctx->device); cudaFree(w->d_base); }
+    if (w->ctx && !w->in_arena) { cudaSetDevice(w->ctx->device); cudaFree(w->d_base); }
     delete w;
     return SW_OK;
 }
@@ -146,7 +172,16 @@ static int check_params(sw_ctx *ctx, const sw_params *pm, int strategy)
     return SW_OK;
 }
 
+static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, bool use_arena, sw_workload **out);
+
 extern "C" int sw_workload_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, sw_workload **out)
+{
+    if (!ctx) return SW_ERR_ARG;
+    std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+    return wl_create(ctx, fp, cigar_stride, false, out);
+}
+
+static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, bool use_arena, sw_workload **out)
 {
     if (!ctx || !fp || !out) return SW_ERR_ARG;
     *out = nullptr;
@@ -186,14 +221,14 @@ extern "C" int sw_workload_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t 
         r.ref_len = l1; r.alt_len = l2; r.out = (int32_t)p; r.pad = 0;
         recs[c].push_back(r);
         max_sum = std::max(max_sum, l1 + l2);
-        const int kh = CLASS_KH[c], stripes = (l1 + 32 * kh - 1) / (32 * kh);
-        w->class_bt_stride[c] = std::max<int64_t>(w->class_bt_stride[c], (int64_t)stripes * (l2 + 31) * 32);
-        w->bt_bytes += (int64_t)stripes * (l2 + std::min(32, (l1 + kh - 1) / kh) - 1) * 128;
+        const int kh = CLASS_KH[c], nw = (kh + 7) / 8;
+        w->class_bt_stride[c] = std::max<int64_t>(w->class_bt_stride[c], (int64_t)(l2 + 31) * nw * 32);
+        w->bt_bytes += (int64_t)l2 * ((l1 + kh - 1) / kh) * nw * 4;        // one word per active lane, word slot and step
     }
     w->elems_stride = max_sum + 8;
     std::vector<PairRec> all;
     all.reserve((size_t)n);
-    int64_t bt_words = 1, warps_max = 1;
+    int64_t bt_words = 0, warps_sum = 0;
     for (int c = 0; c < N_CLASSES; ++c) {
         std::stable_sort(recs[c].begin(), recs[c].end(), [](const PairRec &a, const PairRec &b) {
             return (int64_t)a.ref_len * a.alt_len > (int64_t)b.ref_len * b.alt_len;
@@ -205,8 +240,11 @@ extern "C" int sw_workload_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t 
         const int64_t want = ((int64_t)recs[c].size() + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
         w->class_grid[c] = (int)std::max<int64_t>(1, std::min(full, want));
         const int64_t warps = (int64_t)w->class_grid[c] * WARPS_PER_BLOCK;
-        bt_words = std::max(bt_words, warps * w->class_bt_stride[c]);
-        warps_max = std::max(warps_max, warps);
+        if (recs[c].empty()) continue;
+        w->class_bt_off[c] = bt_words;
+        w->class_elems_off[c] = warps_sum * w->elems_stride;
+        bt_words += warps * w->class_bt_stride[c];
+        warps_sum += warps;
     }
 
     auto fail = [&](int code) { sw_workload_destroy(w); return code; };
@@ -220,11 +258,24 @@ extern "C" int sw_workload_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t 
         {(void **)&w->d_counters, 64 * 4},
         {(void **)&w->d_cigar, np * (size_t)cigar_stride},
         {(void **)&w->d_bt, (size_t)bt_words * 4},
-        {(void **)&w->d_elems, (size_t)(warps_max * w->elems_stride) * sizeof(int2)},
+        {(void **)&w->d_elems, (size_t)(warps_sum * w->elems_stride) * sizeof(int2)},
     };
     size_t total = 0;
     for (const Piece &p : pieces) total += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255;
-    cudaError_t e = cudaMalloc((void **)&w->d_base, total);
+    cudaError_t e = cudaSuccess;
+    if (use_arena) {
+        // steady-state calls never pay cudaMalloc / cudaFree (both synchronise the device)
+        w->in_arena = true;
+        if (ctx->arena_cap < total) {
+            cudaFree(ctx->arena);
+            ctx->arena = nullptr;
+            ctx->arena_cap = 0;
+            if ((e = cudaMalloc((void **)&ctx->arena, total + total / 4)) == cudaSuccess) ctx->arena_cap = total + total / 4;
+        }
+        w->d_base = ctx->arena;
+    } else {
+        e = cudaMalloc((void **)&w->d_base, total);
+    }
     if (e != cudaSuccess) {
         ctx->error = std::string("cudaMalloc: ") + cudaGetErrorString(e);
         return fail(e == cudaErrorMemoryAllocation ? SW_ERR_NOMEM : SW_ERR_CUDA);
@@ -252,6 +303,8 @@ static int wl_launch(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strat
     SW_TRY(ctx, cudaSetDevice(ctx->device));
     SW_TRY(ctx, cudaMemsetAsync(w->d_counters, 0, 64 * 4, st));
     SW_TRY(ctx, cudaEventRecord(ctx->ev[0], st));
+    SW_TRY(ctx, cudaEventRecord(ctx->ev_fork, st));
+    for (int k = 0; k < sw_ctx::N_SIDE; ++k) SW_TRY(ctx, cudaStreamWaitEvent(ctx->side[k], ctx->ev_fork, 0));
     w->launches = 0;
     // longest-running class first: its tail is covered by the blocks of the next
     for (int c = N_CLASSES - 1; c >= 0; --c) {
@@ -264,13 +317,18 @@ static int wl_launch(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strat
         P.counter = w->d_counters + c;
         P.match = pm->match; P.mismatch = pm->mismatch; P.open = pm->open; P.extend = pm->extend;
         P.strategy = strategy;
-        P.bt = w->d_bt; P.bt_stride = w->class_bt_stride[c];
-        P.elems = w->d_elems; P.elems_stride = w->elems_stride;
+        P.one = 1;
+        P.bt = w->d_bt + w->class_bt_off[c]; P.bt_stride = w->class_bt_stride[c];
+        P.elems = w->d_elems + w->class_elems_off[c]; P.elems_stride = w->elems_stride;
         P.score = w->d_score; P.offset = w->d_offset; P.cigar_len = w->d_cigar_len;
         P.cigar = w->d_cigar; P.cigar_stride = w->cigar_stride;
-        kernel_for(c)<<<w->class_grid[c], WARPS_PER_BLOCK * 32, WARPS_PER_BLOCK * sizeof(WarpSmem), st>>>(P);
+        kernel_for(c)<<<w->class_grid[c], WARPS_PER_BLOCK * 32, WARPS_PER_BLOCK * sizeof(WarpSmem), ctx->side[w->launches % sw_ctx::N_SIDE]>>>(P);
         SW_TRY(ctx, cudaGetLastError());
         ++w->launches;
+    }
+    for (int k = 0; k < sw_ctx::N_SIDE; ++k) {
+        SW_TRY(ctx, cudaEventRecord(ctx->ev_join[k], ctx->side[k]));
+        SW_TRY(ctx, cudaStreamWaitEvent(st, ctx->ev_join[k], 0));
     }
     SW_TRY(ctx, cudaEventRecord(ctx->ev[1], st));
     return SW_OK;
@@ -293,7 +351,7 @@ static void fill_stats(sw_ctx *ctx, sw_workload *w, sw_stats *stats)
 extern "C" int sw_workload_run(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strategy, sw_stats *stats)
 {
     if (!ctx || !w || w->ctx != ctx) return SW_ERR_ARG;
-    std::lock_guard<std::mutex> lk(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lk(ctx->mu);
     int rc = check_params(ctx, pm, strategy);
     if (rc != SW_OK) return rc;
     rc = wl_launch(ctx, w, pm, strategy);
@@ -307,7 +365,7 @@ extern "C" int sw_workload_results(sw_ctx *ctx, sw_workload *w, int32_t *score, 
                                    int32_t *cigar_len)
 {
     if (!ctx || !w || w->ctx != ctx) return SW_ERR_ARG;
-    std::lock_guard<std::mutex> lk(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lk(ctx->mu);
     SW_TRY(ctx, cudaSetDevice(ctx->device));
     const size_t n = (size_t)w->n_pairs;
     if (n == 0) return SW_OK;
@@ -327,12 +385,14 @@ extern "C" int sw_align_flat(sw_ctx *ctx, const sw_flat_pairs *fp, const sw_para
     int rc = check_params(ctx, pm, strategy);
     if (rc != SW_OK) return rc;
     if (fp->n_pairs && (!cigar || !cigar_len)) { ctx->error = "NULL cigar output"; return SW_ERR_ARG; }
+    std::lock_guard<std::recursive_mutex> lk(ctx->mu);
     struct timespec t0, t1;
     clock_gettime(CLOCK_MONOTONIC, &t0);
     sw_workload *w = nullptr;
-    rc = sw_workload_create(ctx, fp, cigar_stride, &w);
+    rc = wl_create(ctx, fp, cigar_stride, true, &w);
     if (rc != SW_OK) return rc;
     sw_stats st;
+    memset(&st, 0, sizeof st);
     rc = sw_workload_run(ctx, w, pm, strategy, &st);
     if (rc == SW_OK) rc = sw_workload_results(ctx, w, score, offset, cigar, cigar_len);
     sw_workload_destroy(w);

@@ -3,25 +3,39 @@
 // Computes what smithWatermanBackTrack + getCIGAR compute
 // (tools/GKL/src/main/native/smithwaterman/PairWiseSW.h:40-263, :265-412), bit for bit:
 //
-//   * Wavefront over a stripe of 32 * KH rows: lane l owns rows base + l*KH .. + KH-1 in registers
-//     (H and E of the previous column), works on column step - l, and hands the H and F of its bottom
-//     row to lane l + 1 with __shfl_up_sync.  The reference sweeps anti-diagonals with 8/16-wide
-//     vectors through three memory arrays (:98-194); here the diagonal state never leaves registers.
-//   * ref longer than one stripe: the bottom row of a stripe (H, F per column) stays in shared
-//     memory for the next stripe.
-//   * Backtrack: 4 bits per cell (MATCH/INSERT/DELETE + the two *_EXT flags, :21-25), the KH cells a
-//     lane computes in one step packed into one 32-bit word, stored at [stripe][step][lane] -- one
-//     coalesced 128-byte line per warp and step.  The reference writes 16 bits per cell (:170).
+//   * Wavefront: lane l owns rows l*KH + 1 .. l*KH + KH in registers (H and E of the previous
+//     column), works on column step - l, and hands the H and F of its bottom row to lane l + 1 with
+//     __shfl_up_sync.  KH is a template parameter; a pair runs in the smallest class with
+//     32 * KH >= len1 (KH <= 32 covers MAX_SEQ_LEN = 1024), so most lanes hold real rows.  The
+//     reference sweeps anti-diagonals with 8/16-wide vectors through three memory arrays (:98-194);
+//     here the diagonal state never leaves registers.
+//   * max(a + b, c) is Blackwell's fused VIADDMNMX (__viaddmax_s32): three of them per cell.
+//   * Backtrack: 4 bits per cell (MATCH/INSERT/DELETE + the two *_EXT flags, :21-25), eight cells of
+//     a lane per 32-bit word, stored at [step][word][lane] -- coalesced 128-byte lines per warp and
+//     step.  The reference writes 16 bits per cell (:170).
 //   * Last row / last column scores go to shared memory; the best cell is chosen afterwards in the
 //     reference's visiting order (:209-236): a warp-wide maximum, then the tie rule applied to the
 //     cells that reach it, in anti-diagonal order.
-//   * Traceback and CIGAR formatting (:265-412) by the warp on the backtrack words it just wrote.
+//   * Traceback and CIGAR formatting (:265-412) by the warp on the backtrack words it just wrote,
+//     through a 32-step window of words fetched with one warp-wide load.
 #ifndef SW_KERNELS_CUH
 #define SW_KERNELS_CUH
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+#include <utility>
+
 namespace sw {
+
+// compile-time loop: the body sees its index as a constant expression (immediate operands of inline PTX)
+template <int... Is, class F>
+__device__ __forceinline__ void static_for_impl(std::integer_sequence<int, Is...>, F &&f)
+{
+    (f(std::integral_constant<int, Is>{}), ...);
+}
+template <int N, class F>
+__device__ __forceinline__ void static_for(F &&f) { static_for_impl(std::make_integer_sequence<int, N>{}, f); }
 
 static const int WARPS_PER_BLOCK = 4;
 static const int MAX_LEN = 1024;
@@ -45,6 +59,7 @@ struct Params {
     int32_t ntasks;
     int32_t *counter;           // queue head
     int32_t match, mismatch, open, extend, strategy;
+    int32_t one;                // = 1, opaque to the compiler: see fma_add()
     uint32_t *bt;               // per-warp backtrack scratch
     int64_t bt_stride;          // words per warp
     int2 *elems;                // per-warp CIGAR element scratch
@@ -54,26 +69,65 @@ struct Params {
     int32_t cigar_stride;
 };
 
-// per-warp shared memory: stripe boundary H / F, last row, last column, alt bytes
+// per-warp shared memory: last row, last column, alt bytes
 struct __align__(16) WarpSmem {
-    int32_t hb[MAX_LEN + 1], fb[MAX_LEN + 1];
     int32_t lastrow[MAX_LEN + 1], lastcol[MAX_LEN + 1];
     uint8_t alt[MAX_LEN + 16];
 };
 
 __device__ __forceinline__ int iabs(int x) { return x < 0 ? -x : x; }
 
+// The DP loop saturates the integer ALU pipe (ncu: 92 % of cycles active) while the FMA pipe, which
+// also executes IMAD, idles.  a * one + b with `one` a kernel parameter equal to 1 cannot be folded by
+// ptxas into an IADD, so these additions issue as IMAD on the FMA pipe.
+__device__ __forceinline__ int32_t fma_add(int32_t a, int32_t one, int32_t b)
+{
+    int32_t r;
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(one), "r"(b));
+    return r;
+}
+
+// Backtrack nibble of one cell (PairWiseSW.h:8-11,18-20,27-35) added into `word` at bit SHIFT: four
+// compares on the ALU pipe, four predicated IMADs on the FMA pipe.
+//   INSERT_EXT  <=> !(open_h > ext_h) <=> max(open_h, ext_h) == ext_h
+//   DELETE_EXT  likewise for the vertical gap
+//   DELETE      <=> f11 > max(h0, e11)            (overrides INSERT, :33)
+//   INSERT      <=> e11 > h0 and not DELETE        (:29-31)
+template <int SHIFT>
+__device__ __forceinline__ void bt_flags(uint32_t &word, int32_t one, int32_t e11, int32_t ext_h, int32_t f11,
+                                         int32_t ext_v, int32_t h0, int32_t h1)
+{
+    asm("{\n\t"
+        ".reg .pred pa, pb, pc, pd;\n\t"
+        "setp.eq.s32 pa, %1, %2;\n\t"
+        "setp.eq.s32 pb, %3, %4;\n\t"
+        "setp.gt.s32 pc, %3, %6;\n\t"
+        "setp.gt.and.s32 pd, %1, %5, !pc;\n\t"
+        "@pa mad.lo.u32 %0, %7, %8, %0;\n\t"
+        "@pb mad.lo.u32 %0, %7, %9, %0;\n\t"
+        "@pc mad.lo.u32 %0, %7, %10, %0;\n\t"
+        "@pd mad.lo.u32 %0, %7, %11, %0;\n\t"
+        "}"
+        : "+r"(word)
+        : "r"(e11), "r"(ext_h), "r"(f11), "r"(ext_v), "r"(h0), "r"(h1), "r"(one),
+          "n"((uint32_t)F_INSERT_EXT << SHIFT), "n"((uint32_t)F_DELETE_EXT << SHIFT),
+          "n"((uint32_t)OP_DELETE << SHIFT), "n"((uint32_t)OP_INSERT << SHIFT));
+}
+
+// KH rows per lane; a pair runs in the smallest class with 32 * KH >= len1, so one stripe of the
+// wavefront always covers the whole matrix (MAX_LEN = 32 * 32) and most lanes hold real rows.
 template <int KH>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 sw_align_kernel(const Params P)
 {
+    static_assert(KH >= 1 && KH <= 32, "one stripe must cover MAX_LEN rows");
+    constexpr int NW = (KH + 7) / 8;                     // backtrack words per lane and step
     extern __shared__ __align__(16) uint8_t smem_raw[];
     WarpSmem &S = reinterpret_cast<WarpSmem *>(smem_raw)[threadIdx.x >> 5];
     const int lane = threadIdx.x & 31;
     const int warp_global = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
     uint32_t *bt = P.bt + (int64_t)warp_global * P.bt_stride;
     int2 *elems = P.elems + (int64_t)warp_global * P.elems_stride;
-    constexpr int STRIPE = 32 * KH;
     const bool lead = (P.strategy == ST_INDEL || P.strategy == ST_LEADING_INDEL);
 
     for (;;) {
@@ -87,15 +141,9 @@ sw_align_kernel(const Params P)
         __syncwarp();
         for (int k = lane; k < ncol; k += 32) S.alt[k] = P.alt_pool[pr.alt_off + k];
         __syncwarp();
-
-        const int nstripes = (nrow + STRIPE - 1) / STRIPE;
-        const int T = ncol + 31;                         // steps per stripe (stride of the backtrack words)
-        for (int s = 0; s < nstripes; ++s) {
-            const int base = s * STRIPE;                 // rows base + 1 .. base + STRIPE
-            const int i0 = base + lane * KH + 1;         // first row of this lane (1-based)
-            const int rows_here = min(STRIPE, nrow - base);
-            const int lanes_used = (rows_here + KH - 1) / KH;
-            const bool last_stripe = (s == nstripes - 1);
+        {
+            const int i0 = lane * KH + 1;                // first row of this lane (1-based)
+            const int lanes_used = (nrow + KH - 1) / KH;
             // column-0 boundary (:196-205): H(i, 0) = open + (i - 1) * extend or 0; E(i, 0) = LOW (:207)
             int32_t Hl[KH], E[KH];
             uint32_t c1[KH];
@@ -107,62 +155,50 @@ sw_align_kernel(const Params P)
                 c1[p] = (i <= nrow) ? (uint32_t)seq1[i - 1] : 0x100u;    // padding rows match nothing
             }
             // H(i0 - 1, 0): diagonal neighbour of the lane's first row at column 1
-            int32_t Hd_next = (i0 - 1 == 0) ? 0 : (lead ? P.open + (i0 - 2) * P.extend : 0);
+            int32_t Hd_next = (lane == 0) ? 0 : (lead ? P.open + (i0 - 2) * P.extend : 0);
             int32_t Hbot = 0, Fbot = SW_LOW_INIT;
             const int pr_row = (nrow - 1) % KH;          // register slot of row nrow in its lane
-            const int lr_lane = ((nrow - 1) % STRIPE) / KH;
+            const int lr_lane = (nrow - 1) / KH;
             const int steps = ncol + lanes_used - 1;
             for (int st = 0; st < steps; ++st) {
                 const int j = st - lane + 1;             // this lane's column (1-based)
                 int32_t Ht = __shfl_up_sync(FULL, Hbot, 1);
                 int32_t Ft = __shfl_up_sync(FULL, Fbot, 1);
-                if (lane == 0) {
-                    const int jj = min(max(j, 0), ncol);
-                    if (s == 0) { Ht = lead ? P.open + (jj - 1) * P.extend : 0; Ft = SW_LOW_INIT; }   // row 0 (:196-206)
-                    else        { Ht = S.hb[jj]; Ft = S.fb[jj]; }
-                }
+                if (lane == 0) { Ht = lead ? P.open + (j - 1) * P.extend : 0; Ft = SW_LOW_INIT; }   // row 0 (:196-206)
                 if (j >= 1 && j <= ncol && lane < lanes_used) {
                     const uint32_t c2 = S.alt[j - 1];
                     int32_t Hd = Hd_next;
                     Hd_next = Ht;
-                    uint32_t word = 0;
-                    int32_t hsel = 0;
+                    uint32_t word[NW];
 #pragma unroll
-                    for (int p = 0; p < KH; ++p) {
-                        // MAIN_CODE (:3-37)
-                        const int32_t open_h = Hl[p] + P.open, ext_h = E[p] + P.extend;
-                        const int32_t e11 = max(open_h, ext_h);
-                        uint32_t b = (open_h > ext_h) ? 0u : (uint32_t)F_INSERT_EXT;
-                        const int32_t open_v = Ht + P.open, ext_v = Ft + P.extend;
-                        const int32_t f11 = max(ext_v, open_v);
-                        b |= (open_v > ext_v) ? 0u : (uint32_t)F_DELETE_EXT;
-                        const int32_t m11 = Hd + ((c1[p] == c2) ? P.match : P.mismatch);
-                        int32_t h11 = max(m11, SW_MIN_CUTOFF);
-                        b |= (e11 > h11) ? (uint32_t)OP_INSERT : 0u;
-                        h11 = max(h11, e11);
-                        if (f11 > h11) b = (b & ~3u) | (uint32_t)OP_DELETE;
-                        h11 = max(h11, f11);
-                        word |= b << (4 * p);
+                    for (int q = 0; q < NW; ++q) word[q] = 0;
+                    int32_t hsel = 0;
+                    static_for<KH>([&](auto pc) {
+                        constexpr int p = decltype(pc)::value;
+                        // MAIN_CODE (:3-37); max(a + b, c) is one VIADDMNMX
+                        const int32_t ext_h = fma_add(E[p], P.one, P.extend);
+                        const int32_t e11 = __viaddmax_s32(Hl[p], P.open, ext_h);
+                        const int32_t ext_v = fma_add(Ft, P.one, P.extend);
+                        const int32_t f11 = __viaddmax_s32(Ht, P.open, ext_v);
+                        const int32_t h0 = __viaddmax_s32(Hd, (c1[p] == c2) ? P.match : P.mismatch, SW_MIN_CUTOFF);
+                        const int32_t h1 = max(h0, e11);
+                        const int32_t h11 = max(h1, f11);
+                        bt_flags<4 * (p % 8)>(word[p / 8], P.one, e11, ext_h, f11, ext_v, h0, h1);
                         Hd = Hl[p];
                         Ht = h11; Ft = f11;
                         Hl[p] = h11; E[p] = e11;
                         if (p == pr_row) hsel = h11;
-                    }
+                    });
                     Hbot = Ht; Fbot = Ft;
-                    bt[((int64_t)s * T + st) * 32 + lane] = word;
-                    if (!last_stripe && lane == 31) { S.hb[j] = Hbot; S.fb[j] = Fbot; }
-                    if (last_stripe && lane == lr_lane) S.lastrow[j] = hsel;
+#pragma unroll
+                    for (int q = 0; q < NW; ++q) bt[((int64_t)st * NW + q) * 32 + lane] = word[q];
+                    if (lane == lr_lane) S.lastrow[j] = hsel;
                     if (j == ncol) {
 #pragma unroll
                         for (int p = 0; p < KH; ++p)
                             if (i0 + p <= nrow) S.lastcol[i0 + p] = Hl[p];
                     }
                 }
-            }
-            __syncwarp();
-            if (!last_stripe && lane == 0) {             // H(base + STRIPE, 0) for the next stripe's lane 0
-                S.hb[0] = lead ? P.open + (base + STRIPE - 1) * P.extend : 0;
-                S.fb[0] = SW_LOW_INIT;
             }
             __syncwarp();
         }
@@ -218,11 +254,21 @@ sw_align_kernel(const Params P)
         };
         if (j < ncol) push(ST_SOFTCLIP, ncol - j);
         int state = 0;
+        // window: lane L holds the backtrack word of (w_ln, w_q) at step w_st - L, so a run of moves
+        // inside one lane's 8-row word costs one round trip to L2 instead of one per move
+        int w_ln = -1, w_q = -1, w_st = 0;
+        uint32_t wv = 0;
         while (i > 0 && j > 0) {
-            const int r = (i - 1) % STRIPE, s = (i - 1) / STRIPE;
-            const int ln = r / KH, p = r % KH;
-            const uint32_t w = __ldcg(bt + ((int64_t)s * T + (j - 1 + ln)) * 32 + ln);
-            const int btr = (int)((w >> (4 * p)) & 15u);
+            const int r = i - 1;
+            const int ln = r / KH, p = r % KH, q = p / 8;
+            const int st = j - 1 + ln;
+            if (ln != w_ln || q != w_q || st > w_st || st < w_st - 31) {
+                w_ln = ln; w_q = q; w_st = st;
+                const int s2 = st - lane;
+                wv = (s2 >= 0) ? __ldcg(bt + ((int64_t)s2 * NW + q) * 32 + ln) : 0u;
+            }
+            const uint32_t w = __shfl_sync(FULL, wv, w_st - st);
+            const int btr = (int)((w >> (4 * (p % 8))) & 15u);
             if (state == F_INSERT_EXT) { --j; ++cur_len; state = btr & F_INSERT_EXT; }
             else if (state == F_DELETE_EXT) { --i; ++cur_len; state = btr & F_DELETE_EXT; }
             else {

@@ -28,11 +28,9 @@ class SwResult:
 
     @property
     def cigars(self):
-        out = []
-        for p, n in enumerate(self.cigar_len):
-            assert n >= 0, "cigar did not fit the stride"
-            out.append(self.buf[p * self.stride:p * self.stride + n].tobytes().decode())
-        return out
+        # None where the CIGAR did not fit the stride (cigar_len = -1 - needed), as the product reports it
+        return [self.buf[p * self.stride:p * self.stride + n].tobytes().decode() if n >= 0 else None
+                for p, n in enumerate(self.cigar_len)]
 
 
 def _run(fn, extra, pairs, params, strategy, nthreads, stride):
