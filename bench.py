@@ -322,7 +322,11 @@ def main():
                     "includes": "host planning + H2D from pageable host buffers + kernels + D2H of the 8 B/pair results into the caller's buffer; chunks of batches pipelined (plan + upload of one under the kernels of the other)"},
             "gpu_launches": int(st["n_launches"]) * args.steps,
             "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                         "traffic": None,
+                         "traffic": ncu_traffic("phmm") if (fast and args.workload == "c2") else None,
+                         "hbm": {"algorithmic_bytes_per_step": int(h2d + 8 * fb.n_pairs),
+                                 "note": "inputs as uploaded + 8 B per result; `traffic` = dram__bytes_read.sum + "
+                                         "dram__bytes_write.sum over the same launches of one step from the ncu --set full "
+                                         "capture in profiles/ (C2, one GPU); both are ~1e-3 of what HBM moves in the step time"},
                          "kernel": ("phmm_forward_hp_kernel<KH, LANES>" if fast else "phmm_forward_kernel<float, KH, LANES>")
                                    + " (all FP32 class instantiations of the step together, rank 0)",
                          "how": "12 flop/cell x cells / CUDA-event time of the FP32 launches; peak = 2 x FFMA lane-ops/s "
@@ -340,6 +344,14 @@ def main():
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_traffic(tag):
+    """DRAM bytes per step of the kernel set `achieved` covers, from the committed ncu --set full capture."""
+    try:
+        return int(json.load(open(os.path.join(ROOT, "profiles", "r1_v9_dram_traffic.json")))[tag]["traffic_bytes_per_step"])
+    except Exception:
+        return None
 
 
 if __name__ == "__main__":

@@ -30,6 +30,16 @@ from genomicsbench_palisade_b200 import sw, sw_pairs  # noqa: E402
 PARAMS = (200, -150, -260, -11)       # GATK's haplotype-to-reference parameters (SmithWatermanUnitTest.java:48)
 
 
+def ncu_traffic():
+    """DRAM bytes per step (all sw_align_kernel launches) from the committed ncu --set full capture of this
+    command at its default size; above the algorithmic bytes because the traceback window re-reads 32 lines per
+    refill and partially filled 128-byte lines are written whole."""
+    try:
+        return int(json.load(open(os.path.join(ROOT, "profiles", "r1_v9_dram_traffic.json")))["sw"]["traffic_bytes_per_step"])
+    except Exception:
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=5)
@@ -73,7 +83,8 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6500.0))
     algo_bytes = st["bt_bytes"] + int(ps.ref_len.sum()) + int(ps.alt_len.sum()) + ps.n_pairs * (12 + 16)
     out["roofline"] = {"bound": "hbm", "achieved": algo_bytes / ms_step / 1e6, "peak": peak, "unit": "GB/s",
-                       "frac": algo_bytes / ms_step / 1e6 / peak, "traffic": None,
+                       "frac": algo_bytes / ms_step / 1e6 / peak, "traffic": ncu_traffic(),
+                       "algorithmic_bytes_per_step": int(algo_bytes),
                        "kernel": "sw_align_kernel<KH> (all classes of the step together)",
                        "how": "algorithmic bytes (4-bit backtrack cells as stored: one 32-bit word per lane and step, "
                               "+ sequences + results) / CUDA-event time; peak = MEASURED_PEAKS.json hbm_gbs"
