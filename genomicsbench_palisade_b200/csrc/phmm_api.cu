@@ -132,6 +132,7 @@ const int INTS_COUNTER = 0;                       // one queue head per launch, 
 const int INTS_NTASKS = 64;                       // per FP32 class
 const int INTS_RESC = 128;                        // [MAX_KH_SCALAR + 1]
 const int INTS_GUARD = 128 + 16;
+const int INTS_GUARD64 = 128 + 32;                // fast FP64 kernels: non-finite sums, re-run by the exact FP64 kernel
 const int INTS_TOTAL = 192;
 
 #define CUDA_TRY(ctx, expr)                                                                   \
@@ -416,7 +417,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
         tot += P.resc_cap[k];
     }
     w->resc_total = tot;
-    const bool need_resc = (w->precision != 2);   // mode 1 still needs the fast kernel's guard list
+    const bool need_resc = true;   // mode 1 needs the fast FP32 kernel's guard list, mode 2 the fast FP64 kernel's
 
     const int64_t pool_len = P.pool_len;
     w->pool_stride = (pool_len + 255) & ~(int64_t)255;
@@ -594,6 +595,9 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     pd.init_const = t.init_d; pd.log10_init = t.log10_init_d;
     pd.out = w->d_out; pd.raw32 = w->d_raw32; pd.raw64 = w->d_raw64; pd.rescued = w->d_rescued;
     pd.mode = mode;
+    // fast FP64 kernels hand non-finite sums to the exact ones through the (by then consumed) guard list storage
+    pd.guard = fast64 ? w->d_guard : nullptr; pd.guard_count = w->d_ints + INTS_GUARD64;
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) pd.resc_off[k] = w->resc_off[k];
     pf.scratch = reinterpret_cast<float *>(w->d_scratch); pf.scratch_stride = 2 * w->scratch_stride;   // in floats
     pd.scratch = w->d_scratch; pd.scratch_stride = w->scratch_stride;
 
@@ -699,6 +703,25 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
             pd.ntasks_ptr = w->d_ints + INTS_RESC + kh;
             pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
             if (!prepare((const void *)k, kh ? kh : LONG_KH, w->resc_cap[kh], kh == 0, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, ks>>>(pd);
+            CUDA_TRY(ctx, cudaGetLastError());
+            ++launches;
+        }
+        CUDA_TRY(ctx, join());
+    }
+    // ---- fast FP64 kernels only: non-finite sums re-run by the bit-exact FP64 kernel --------------
+    if (mode != 1 && fast64) {
+        pd.guard = nullptr;
+        CUDA_TRY(ctx, fork());
+        for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
+            if (w->resc_cap[kh] == 0) continue;
+            if (counter_slot >= 60) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
+            CUDA_TRY(ctx, side_stream(&ks));
+            KernelF64 k = kh ? lookup_f64(kh, false) : lookup_f64_long(false);
+            pd.tasks = w->d_guard + w->resc_off[kh];
+            pd.ntasks_ptr = w->d_ints + INTS_GUARD64 + kh;
+            pd.counter = w->d_ints + INTS_COUNTER + counter_slot++;
+            if (!prepare((const void *)k, kh ? kh : LONG_KH, std::min<int64_t>(w->resc_cap[kh], 256), kh == 0, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
             k<<<grid, WARPS_PER_BLOCK * 32, smem, ks>>>(pd);
             CUDA_TRY(ctx, cudaGetLastError());
             ++launches;

@@ -171,8 +171,24 @@ __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float 
 
 template <bool FAST>
 __device__ __forceinline__ void emit_result(const KernelParams<double> &P, double res, int64_t oidx,
-                                            int64_t, int, int, int, int, int)
+                                            int64_t hap_stream_off, int hap_len, int hap_idx,
+                                            int out_rel, int rid, int rslen)
 {
+    // Fast FP64 kernel (scaled recurrence): X / sigma can overflow for exotic gap-continuation
+    // penalties; a non-finite sum is re-run by the bit-exact FP64 kernel of the read's class.
+    if (FAST && P.guard && !(res <= 1.7976931348623157e+308)) {
+        Task nt;
+        nt.stream_off = hap_stream_off;
+        nt.ncols = hap_len + SEP_COLS;
+        nt.hap0 = hap_idx;
+        nt.out0 = out_rel;
+        nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
+        nt.nh = 1;
+        const int ci = rescue_class(rslen);
+        const int k = atomicAdd(&P.guard_count[ci], 1);
+        P.guard[P.resc_off[ci] + k] = nt;
+        return;
+    }
     // :75 (and :109)
     P.raw64[oidx] = res;
     P.out[oidx] = __dsub_rn(log10(res), P.log10_init);
@@ -192,7 +208,7 @@ phmm_forward_kernel(const KernelParams<T> P)
     constexpr int VL = O::VL;
     // Scaled recurrence of the fast FP32 single-pass kernels (6 + NTOP / KH packed FP instructions
     // per cell instead of 8; see "scaled recurrence" in the cell update below).
-    constexpr bool SCALED = FAST && !LONG && (sizeof(T) == 4);
+    constexpr bool SCALED = FAST && !LONG;      // FP32 and FP64: a non-finite sum goes to the bit-exact kernel
     constexpr int NTOP = (KH + 3) / 4;                 // groups of chained rows per thread
     constexpr int GRP = (KH + NTOP - 1) / NTOP;        // rows per group (<= 4): group tops at p % GRP == 0
     constexpr int ROWS = KH * LANES;          // read rows per pass

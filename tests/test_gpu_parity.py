@@ -245,6 +245,14 @@ def test_fast_kernel_with_exotic_gap_penalties():
         out = eng.compute(fb)
         eng.close()
         assert same_or_close(out, oracle.run_port(fb, mode=1).out, RTOL_FP32)
+        # the fast FP64 kernels use the same rescaling; their overflows (X / sigma beyond 1.8e308 with
+        # the 2^1020 initial constant: GCP above ~Q60) come back through the bit-exact FP64 kernel
+        res64, _ = run(fb, fast=True, fast64=True)
+        check(res64, ref.out, ref.raw32, ref.raw64, ref.rescued, False, False)
+        eng = phmm.PairHMM(precision=phmm.DOUBLE_ONLY, fast64=True)
+        out = eng.compute(fb)
+        eng.close()
+        assert same_or_close(out, oracle.run_port(fb, mode=2).out, RTOL_FP64)
     assert guard_total > 0      # at least one case must have exercised the overflow path
 
 
