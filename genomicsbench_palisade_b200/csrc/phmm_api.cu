@@ -549,7 +549,9 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
 
 // Queues every kernel of the workload on the stream set `ss` (after `wait_for`, when given) and
 // records the timing events.  Does not wait.
-static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t wait_for)
+// fallback64 == nullptr: the whole step.  Otherwise only the rare last phase: counts per class of pairs whose
+// fast FP64 sum was non-finite (read back by wl_finish), re-run by the bit-exact FP64 kernels.
+static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t wait_for, const int32_t *fallback64 = nullptr)
 {
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ss.main;
@@ -565,8 +567,10 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     }
 
     // queue heads and list counters back to zero
-    CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_COUNTER, 0, 64 * sizeof(int32_t), st));
-    CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_RESC, 0, 64 * sizeof(int32_t), st));
+    if (!fallback64) {
+        CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_COUNTER, 0, 64 * sizeof(int32_t), st));
+        CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_RESC, 0, 64 * sizeof(int32_t), st));
+    }
 
     KernelParams<float> pf;
     memset(&pf, 0, sizeof pf);
@@ -643,6 +647,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     };
     cudaStream_t ks = st;
 
+    if (!fallback64) {
     CUDA_TRY(ctx, cudaEventRecord(w->ev[0], st));
     // ---- main pass over the planned tasks ---------------------------------------------------
     CUDA_TRY(ctx, fork());
@@ -709,12 +714,18 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
         }
         CUDA_TRY(ctx, join());
     }
+    CUDA_TRY(ctx, cudaEventRecord(w->ev[2], st));
+    w->launches = launches;
+    return PHMM_OK;
+    }
     // ---- fast FP64 kernels only: non-finite sums re-run by the bit-exact FP64 kernel --------------
+    // (launched by wl_finish when the counters say so: the common case pays nothing)
     if (mode != 1 && fast64) {
         pd.guard = nullptr;
+        counter_slot = 48;                 // queue heads zeroed at the start of the step and not used by it
         CUDA_TRY(ctx, fork());
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
-            if (w->resc_cap[kh] == 0) continue;
+            if (fallback64[kh] == 0) continue;
             if (counter_slot >= 60) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
             CUDA_TRY(ctx, side_stream(&ks));
             KernelF64 k = kh ? lookup_f64(kh, false) : lookup_f64_long(false);
@@ -728,19 +739,24 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
         }
         CUDA_TRY(ctx, join());
     }
-    CUDA_TRY(ctx, cudaEventRecord(w->ev[2], st));
-    w->launches = launches;
+    w->launches += launches;
     return PHMM_OK;
 }
 
 // After the stream set has drained: list counters and event times of the last launch.
 static int wl_finish(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, phmm_stats *stats)
 {
-    int32_t counts[32];
+    int32_t counts[48];
     CUDA_TRY(ctx, cudaMemcpyAsync(counts, w->d_ints + INTS_RESC, sizeof counts, cudaMemcpyDeviceToHost, ss.main));
     CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
-    int64_t nres = 0, nguard = 0;
-    for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nres += counts[k]; nguard += counts[16 + k]; }
+    int64_t nres = 0, nguard = 0, n64 = 0;
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nres += counts[k]; nguard += counts[16 + k]; n64 += counts[32 + k]; }
+    if (n64 > 0) {
+        // fast FP64 kernels met non-finite sums (exotic gap-continuation penalties): bit-exact re-run
+        int rc = wl_launch(ctx, w, ss, nullptr, counts + 32);
+        if (rc != PHMM_OK) return rc;
+        CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
+    }
     w->last_rescued = nres;
     w->last_guard = nguard;
     if (stats) {
@@ -800,10 +816,11 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
     static const bool trace = getenv("PHMM_TRACE") != nullptr;
     std::vector<Chunk> chunks;
     {
-        // default: a tenth of the work per chunk, between 4e9 and 2.4e10 cells (1 to 6 ms of kernels:
-        // smaller chunks run the device less efficiently, larger ones expose more of the first
-        // plan + upload); the first one half that size so the device starts early
-        int rc0 = split_batches(ctx, fb, ctx->chunk_cells, 4000000000ll, 24000000000ll, 10, true, &chunks);
+        // default: a fifth of the work per chunk, between 4e9 and 4e10 cells (1 to 10 ms of kernels:
+        // smaller chunks run the device less efficiently -- every chunk has its own phase joins and
+        // kernel tails; measured on C2: 6e9 40.3 ms, 1.2e10 38.5, 2e10 37.7, 4e10 37.2 -- larger ones
+        // expose more of the first plan + upload); the first one half that size so the device starts early
+        int rc0 = split_batches(ctx, fb, ctx->chunk_cells, 4000000000ll, 40000000000ll, 5, true, &chunks);
         if (rc0 != PHMM_OK) return rc0;
     }
     if (chunks.back().p1 > 0 && !out) { ctx->error = "NULL output"; return PHMM_ERR_ARG; }
@@ -820,15 +837,16 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         phmm_workload *w = wl[slot];
         StreamSet &ss = ctx->ss[slot];
         const double t0 = wall_ms();
-        if (w->n_pairs > 0) {
-            // pageable destination: the call returns when the copy is complete
-            CUDA_TRY(ctx, cudaMemcpyAsync(out + chunks[j].p0, w->d_out, (size_t)w->n_pairs * sizeof(double),
-                                          cudaMemcpyDeviceToHost, ss.main));
-        }
+        // counters first: wl_finish re-runs the (rare) pairs the fast FP64 kernels could not finish
         phmm_stats s;
         int r2 = wl_finish(ctx, w, ss, &s);
-        ms_d2h += wall_ms() - t0;
         if (r2 != PHMM_OK) return r2;
+        if (w->n_pairs > 0) {
+            CUDA_TRY(ctx, cudaMemcpyAsync(out + chunks[j].p0, w->d_out, (size_t)w->n_pairs * sizeof(double),
+                                          cudaMemcpyDeviceToHost, ss.main));
+            CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
+        }
+        ms_d2h += wall_ms() - t0;
         if (trace)
             fprintf(stderr, "phmm trace:   chunk %zu done: fp32 %.2f ms fp64 %.2f ms total %.2f ms, %d launches, %lld tasks, t=%.2f\n", j,
                     s.ms_fp32, s.ms_fp64, s.ms_total, s.n_launches, (long long)s.n_tasks, wall_ms() - t_begin);

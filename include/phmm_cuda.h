@@ -113,7 +113,7 @@ typedef struct {
                                     (0 = choose per read length); also env PHMM_FORCE_CLASS=kh,lanes */
 
 #define PHMM_OPT_CHUNK_CELLS 7   /* host-buffer entry points: cells per pipelined chunk of batches
-                                    (0 = default: a tenth of the work, within [4e9, 2.4e10]); also env PHMM_CHUNK_CELLS */
+                                    (0 = default: a fifth of the work, within [4e9, 4e10]); also env PHMM_CHUNK_CELLS */
 
 typedef struct phmm_ctx phmm_ctx;
 typedef struct phmm_workload phmm_workload;
