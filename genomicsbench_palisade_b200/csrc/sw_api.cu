@@ -40,18 +40,27 @@ Kernel kernel_for(int c)
 }
 }  // namespace
 
-struct sw_ctx {
-    int device = 0, sm_count = 0;
+// Streams, events and the grow-only device arena one workload in flight needs.  Class kernels run side by
+// side on the side streams: the tail of one persistent kernel is filled by the blocks of the next.
+struct Slot {
+    static const int N_SIDE = 4;
     cudaStream_t stream = nullptr;
-    static const int N_SIDE = 4;            // class kernels run side by side: the tail of one is filled by the next
     cudaStream_t side[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev[2] = {nullptr, nullptr};
-    uint8_t *arena = nullptr;               // grow-only device arena of the host-buffer entry points
+    uint8_t *arena = nullptr;               // host-buffer entry points: no cudaMalloc / cudaFree per call
     size_t arena_cap = 0;
+};
+
+struct sw_ctx {
+    int device = 0, sm_count = 0;
+    // slot 0 also serves the device-resident workload API; sw_align_flat pipelines chunks of pairs
+    // through both (upload of one chunk under the kernels of the other)
+    static const int N_SLOTS = 2;
+    Slot slot[N_SLOTS];
     int blocks_per_sm[N_CLASSES] = {0};
     std::string error;
-    std::recursive_mutex mu;           // sw_align_flat holds it across create / run / results (the arena is shared)
+    std::recursive_mutex mu;           // sw_align_flat holds it across create / run / results (the arenas are shared)
 };
 
 struct sw_workload {
@@ -72,7 +81,8 @@ struct sw_workload {
     uint32_t *d_bt = nullptr;
     int2 *d_elems = nullptr;
     int launches = 0;
-    bool in_arena = false;               // buffers live in the context arena: nothing to free
+    bool in_arena = false;               // buffers live in the slot's arena: nothing to free
+    Slot *slot = nullptr;
 };
 
 #define SW_TRY(ctx, expr)                                                                      \
@@ -117,13 +127,16 @@ extern "C" int sw_create(int device, sw_ctx **out)
         return SW_ERR_CUDA;
     };
     if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
-    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
-    for (int k = 0; k < 2; ++k)
-        if ((e = cudaEventCreate(&ctx->ev[k])) != cudaSuccess) return bail("cudaEventCreate", e);
-    if ((e = cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-    for (int k = 0; k < sw_ctx::N_SIDE; ++k) {
-        if ((e = cudaStreamCreateWithFlags(&ctx->side[k], cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
-        if ((e = cudaEventCreateWithFlags(&ctx->ev_join[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    for (int j = 0; j < sw_ctx::N_SLOTS; ++j) {
+        Slot &sl = ctx->slot[j];
+        if ((e = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+        for (int k = 0; k < 2; ++k)
+            if ((e = cudaEventCreate(&sl.ev[k])) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&sl.ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        for (int k = 0; k < Slot::N_SIDE; ++k) {
+            if ((e = cudaStreamCreateWithFlags(&sl.side[k], cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+            if ((e = cudaEventCreateWithFlags(&sl.ev_join[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        }
     }
     const int smem = WARPS_PER_BLOCK * (int)sizeof(WarpSmem);
     for (int c = 0; c < N_CLASSES; ++c) {
@@ -142,14 +155,17 @@ extern "C" int sw_destroy(sw_ctx *ctx)
 {
     if (!ctx) return SW_OK;
     cudaSetDevice(ctx->device);
-    for (int k = 0; k < 2; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
-    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
-    for (int k = 0; k < sw_ctx::N_SIDE; ++k) {
-        if (ctx->ev_join[k]) cudaEventDestroy(ctx->ev_join[k]);
-        if (ctx->side[k]) cudaStreamDestroy(ctx->side[k]);
+    for (int j = 0; j < sw_ctx::N_SLOTS; ++j) {
+        Slot &sl = ctx->slot[j];
+        for (int k = 0; k < 2; ++k) if (sl.ev[k]) cudaEventDestroy(sl.ev[k]);
+        if (sl.ev_fork) cudaEventDestroy(sl.ev_fork);
+        for (int k = 0; k < Slot::N_SIDE; ++k) {
+            if (sl.ev_join[k]) cudaEventDestroy(sl.ev_join[k]);
+            if (sl.side[k]) cudaStreamDestroy(sl.side[k]);
+        }
+        cudaFree(sl.arena);
+        if (sl.stream) cudaStreamDestroy(sl.stream);
     }
-    cudaFree(ctx->arena);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return SW_OK;
 }
@@ -172,16 +188,18 @@ static int check_params(sw_ctx *ctx, const sw_params *pm, int strategy)
     return SW_OK;
 }
 
-static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, bool use_arena, sw_workload **out);
+static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, Slot *arena_slot, sw_workload **out);
 
 extern "C" int sw_workload_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, sw_workload **out)
 {
     if (!ctx) return SW_ERR_ARG;
     std::lock_guard<std::recursive_mutex> lk(ctx->mu);
-    return wl_create(ctx, fp, cigar_stride, false, out);
+    return wl_create(ctx, fp, cigar_stride, nullptr, out);
 }
 
-static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, bool use_arena, sw_workload **out)
+// arena_slot: place the buffers in that slot's arena (which must be idle) and use its streams; NULL: own
+// allocation, slot 0's streams.
+static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride, Slot *arena_slot, sw_workload **out)
 {
     if (!ctx || !fp || !out) return SW_ERR_ARG;
     *out = nullptr;
@@ -208,6 +226,7 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
     w->n_pairs = n;
     w->n_cells = cells;
     w->cigar_stride = cigar_stride;
+    w->slot = arena_slot ? arena_slot : &ctx->slot[0];
 
     // ---- classes by rows per lane, tasks longest first ----------------------------------------------
     std::vector<PairRec> recs[N_CLASSES];
@@ -263,16 +282,16 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
     size_t total = 0;
     for (const Piece &p : pieces) total += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255;
     cudaError_t e = cudaSuccess;
-    if (use_arena) {
+    if (arena_slot) {
         // steady-state calls never pay cudaMalloc / cudaFree (both synchronise the device)
         w->in_arena = true;
-        if (ctx->arena_cap < total) {
-            cudaFree(ctx->arena);
-            ctx->arena = nullptr;
-            ctx->arena_cap = 0;
-            if ((e = cudaMalloc((void **)&ctx->arena, total + total / 4)) == cudaSuccess) ctx->arena_cap = total + total / 4;
+        if (arena_slot->arena_cap < total) {
+            cudaFree(arena_slot->arena);
+            arena_slot->arena = nullptr;
+            arena_slot->arena_cap = 0;
+            if ((e = cudaMalloc((void **)&arena_slot->arena, total + total / 4)) == cudaSuccess) arena_slot->arena_cap = total + total / 4;
         }
-        w->d_base = ctx->arena;
+        w->d_base = arena_slot->arena;
     } else {
         e = cudaMalloc((void **)&w->d_base, total);
     }
@@ -282,7 +301,7 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
     }
     size_t off = 0;
     for (const Piece &p : pieces) { *p.ptr = w->d_base + off; off += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255; }
-    cudaStream_t st = ctx->stream;
+    cudaStream_t st = w->slot->stream;
     if (n) {
         if ((e = cudaMemcpyAsync(w->d_ref, fp->ref_pool + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
             (e = cudaMemcpyAsync(w->d_alt, fp->alt_pool + alo, (size_t)(ahi - alo), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
@@ -299,12 +318,13 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
 
 static int wl_launch(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strategy)
 {
-    cudaStream_t st = ctx->stream;
+    Slot &sl = *w->slot;
+    cudaStream_t st = sl.stream;
     SW_TRY(ctx, cudaSetDevice(ctx->device));
     SW_TRY(ctx, cudaMemsetAsync(w->d_counters, 0, 64 * 4, st));
-    SW_TRY(ctx, cudaEventRecord(ctx->ev[0], st));
-    SW_TRY(ctx, cudaEventRecord(ctx->ev_fork, st));
-    for (int k = 0; k < sw_ctx::N_SIDE; ++k) SW_TRY(ctx, cudaStreamWaitEvent(ctx->side[k], ctx->ev_fork, 0));
+    SW_TRY(ctx, cudaEventRecord(sl.ev[0], st));
+    SW_TRY(ctx, cudaEventRecord(sl.ev_fork, st));
+    for (int k = 0; k < Slot::N_SIDE; ++k) SW_TRY(ctx, cudaStreamWaitEvent(sl.side[k], sl.ev_fork, 0));
     w->launches = 0;
     // longest-running class first: its tail is covered by the blocks of the next
     for (int c = N_CLASSES - 1; c >= 0; --c) {
@@ -322,15 +342,15 @@ static int wl_launch(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strat
         P.elems = w->d_elems + w->class_elems_off[c]; P.elems_stride = w->elems_stride;
         P.score = w->d_score; P.offset = w->d_offset; P.cigar_len = w->d_cigar_len;
         P.cigar = w->d_cigar; P.cigar_stride = w->cigar_stride;
-        kernel_for(c)<<<w->class_grid[c], WARPS_PER_BLOCK * 32, WARPS_PER_BLOCK * sizeof(WarpSmem), ctx->side[w->launches % sw_ctx::N_SIDE]>>>(P);
+        kernel_for(c)<<<w->class_grid[c], WARPS_PER_BLOCK * 32, WARPS_PER_BLOCK * sizeof(WarpSmem), sl.side[w->launches % Slot::N_SIDE]>>>(P);
         SW_TRY(ctx, cudaGetLastError());
         ++w->launches;
     }
-    for (int k = 0; k < sw_ctx::N_SIDE; ++k) {
-        SW_TRY(ctx, cudaEventRecord(ctx->ev_join[k], ctx->side[k]));
-        SW_TRY(ctx, cudaStreamWaitEvent(st, ctx->ev_join[k], 0));
+    for (int k = 0; k < Slot::N_SIDE; ++k) {
+        SW_TRY(ctx, cudaEventRecord(sl.ev_join[k], sl.side[k]));
+        SW_TRY(ctx, cudaStreamWaitEvent(st, sl.ev_join[k], 0));
     }
-    SW_TRY(ctx, cudaEventRecord(ctx->ev[1], st));
+    SW_TRY(ctx, cudaEventRecord(sl.ev[1], st));
     return SW_OK;
 }
 
@@ -345,7 +365,7 @@ static void fill_stats(sw_ctx *ctx, sw_workload *w, sw_stats *stats)
     stats->n_launches = w->launches;
     for (int c = 0; c < N_CLASSES; ++c) stats->n_classes += w->class_ntasks[c] > 0;
     float ms = 0.0f;
-    if (w->launches && cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) stats->ms_kernels = ms;
+    if (w->launches && cudaEventElapsedTime(&ms, w->slot->ev[0], w->slot->ev[1]) == cudaSuccess) stats->ms_kernels = ms;
 }
 
 extern "C" int sw_workload_run(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strategy, sw_stats *stats)
@@ -356,7 +376,7 @@ extern "C" int sw_workload_run(sw_ctx *ctx, sw_workload *w, const sw_params *pm,
     if (rc != SW_OK) return rc;
     rc = wl_launch(ctx, w, pm, strategy);
     if (rc != SW_OK) return rc;
-    SW_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    SW_TRY(ctx, cudaStreamSynchronize(w->slot->stream));
     fill_stats(ctx, w, stats);
     return SW_OK;
 }
@@ -369,7 +389,7 @@ extern "C" int sw_workload_results(sw_ctx *ctx, sw_workload *w, int32_t *score, 
     SW_TRY(ctx, cudaSetDevice(ctx->device));
     const size_t n = (size_t)w->n_pairs;
     if (n == 0) return SW_OK;
-    cudaStream_t st = ctx->stream;
+    cudaStream_t st = w->slot->stream;
     if (score) SW_TRY(ctx, cudaMemcpyAsync(score, w->d_score, n * 4, cudaMemcpyDeviceToHost, st));
     if (offset) SW_TRY(ctx, cudaMemcpyAsync(offset, w->d_offset, n * 4, cudaMemcpyDeviceToHost, st));
     if (cigar_len) SW_TRY(ctx, cudaMemcpyAsync(cigar_len, w->d_cigar_len, n * 4, cudaMemcpyDeviceToHost, st));
@@ -388,20 +408,81 @@ extern "C" int sw_align_flat(sw_ctx *ctx, const sw_flat_pairs *fp, const sw_para
     std::lock_guard<std::recursive_mutex> lk(ctx->mu);
     struct timespec t0, t1;
     clock_gettime(CLOCK_MONOTONIC, &t0);
-    sw_workload *w = nullptr;
-    rc = wl_create(ctx, fp, cigar_stride, true, &w);
-    if (rc != SW_OK) return rc;
-    sw_stats st;
-    memset(&st, 0, sizeof st);
-    rc = sw_workload_run(ctx, w, pm, strategy, &st);
-    if (rc == SW_OK) rc = sw_workload_results(ctx, w, score, offset, cigar, cigar_len);
-    sw_workload_destroy(w);
+    // Chunks of consecutive pairs, pipelined through the two slots: the (pageable, hence staged) upload
+    // and the class planning of chunk j + 1 run under the kernels of chunk j; results of chunk j are
+    // copied back when its slot is needed again.  A quarter of the work per chunk, at least 1e9 cells.
+    const int64_t n = fp->n_pairs;
+    if (n < 0 || n > INT32_MAX) { ctx->error = "bad pair count"; return SW_ERR_ARG; }
+    if (n && (!fp->ref_len || !fp->ref_off || !fp->ref_pool || !fp->alt_len || !fp->alt_off || !fp->alt_pool)) {
+        ctx->error = "NULL array in sw_flat_pairs";
+        return SW_ERR_ARG;
+    }
+    if (n == 0) { if (stats) memset(stats, 0, sizeof *stats); return SW_OK; }
+    int64_t total_cells = 0;
+    for (int64_t p = 0; p < n; ++p) {
+        if (fp->ref_len[p] <= 0 || fp->alt_len[p] <= 0) { ctx->error = "sequence of length <= 0"; return SW_ERR_EMPTY_SEQ; }
+        total_cells += (int64_t)fp->ref_len[p] * fp->alt_len[p];
+    }
+    const int64_t per = std::max<int64_t>(1000000000ll, total_cells / 4 + 1);
+    std::vector<int64_t> cut(1, 0);
+    for (int64_t p = 0, acc = 0; p < n; ++p) {
+        acc += (int64_t)fp->ref_len[p] * fp->alt_len[p];
+        const int64_t want = cut.size() == 1 ? per / 2 : per;      // a small first chunk starts the device early
+        if (acc >= want || p == n - 1) { cut.push_back(p + 1); acc = 0; }
+    }
+    if (cut.size() == 1) cut.push_back(0);
+    const size_t nchunks = cut.size() - 1;
+    sw_workload *wl[sw_ctx::N_SLOTS] = {nullptr, nullptr};
+    size_t chunk_of[sw_ctx::N_SLOTS] = {0, 0};
+    sw_stats agg;
+    memset(&agg, 0, sizeof agg);
+    auto retire = [&](int slot) -> int {
+        sw_workload *w = wl[slot];
+        wl[slot] = nullptr;
+        const int64_t p0 = cut[chunk_of[slot]];
+        int r = SW_OK;
+        if (cudaStreamSynchronize(w->slot->stream) != cudaSuccess) { ctx->error = "kernel execution failed"; r = SW_ERR_CUDA; }
+        sw_stats s;
+        if (r == SW_OK) {
+            fill_stats(ctx, w, &s);
+            r = sw_workload_results(ctx, w, score ? score + p0 : nullptr, offset ? offset + p0 : nullptr,
+                                    cigar + p0 * (int64_t)cigar_stride, cigar_len + p0);
+        }
+        if (r == SW_OK) {
+            agg.n_pairs += s.n_pairs; agg.n_cells += s.n_cells; agg.h2d_bytes += s.h2d_bytes; agg.bt_bytes += s.bt_bytes;
+            agg.n_launches += s.n_launches; agg.n_classes = std::max(agg.n_classes, s.n_classes);
+            agg.ms_kernels += s.ms_kernels;
+        }
+        sw_workload_destroy(w);
+        return r;
+    };
+    for (size_t j = 0; j < nchunks && rc == SW_OK; ++j) {
+        const int slot = (int)(j % sw_ctx::N_SLOTS);
+        if (wl[slot]) rc = retire(slot);
+        if (rc != SW_OK) break;
+        chunk_of[slot] = j;
+        sw_flat_pairs sub = *fp;
+        sub.n_pairs = cut[j + 1] - cut[j];
+        sub.ref_len = fp->ref_len + cut[j]; sub.ref_off = fp->ref_off + cut[j];
+        sub.alt_len = fp->alt_len + cut[j]; sub.alt_off = fp->alt_off + cut[j];
+        rc = wl_create(ctx, &sub, cigar_stride, &ctx->slot[slot], &wl[slot]);
+        if (rc == SW_OK) rc = wl_launch(ctx, wl[slot], pm, strategy);
+    }
+    // oldest chunk first
+    for (int k = 0; k < sw_ctx::N_SLOTS; ++k) {
+        int slot = -1;
+        for (int q = 0; q < sw_ctx::N_SLOTS; ++q)
+            if (wl[q] && (slot < 0 || chunk_of[q] < chunk_of[slot])) slot = q;
+        if (slot < 0) break;
+        const int r = retire(slot);
+        if (rc == SW_OK) rc = r;
+    }
     if (rc != SW_OK) return rc;
     clock_gettime(CLOCK_MONOTONIC, &t1);
-    for (int64_t p = 0; p < fp->n_pairs; ++p) st.n_overflow += cigar_len[p] < 0;
-    st.d2h_bytes = fp->n_pairs * (12 + (int64_t)cigar_stride);
-    st.ms_total = (float)((t1.tv_sec - t0.tv_sec) * 1e3 + (t1.tv_nsec - t0.tv_nsec) * 1e-6);
-    if (stats) *stats = st;
+    for (int64_t p = 0; p < n; ++p) agg.n_overflow += cigar_len[p] < 0;
+    agg.d2h_bytes = n * (12 + (int64_t)cigar_stride);
+    agg.ms_total = (float)((t1.tv_sec - t0.tv_sec) * 1e3 + (t1.tv_nsec - t0.tv_nsec) * 1e-6);
+    if (stats) *stats = agg;
     return SW_OK;
 }
 
