@@ -150,6 +150,30 @@ def run_cpu(fb, kind):
     return time.perf_counter() - t
 
 
+def cpu_variants(fb, seconds=4.0):
+    """the reference's AVX-512 and AVX-256 instantiations, FTZ off (as the benchmark ships)
+    and on (as the JNI path sets it), all host threads and one thread; a few seconds each."""
+    import oracle
+    out = {"cpu_model": "", "variants": []}
+    try:
+        out["cpu_model"] = [l.split(":", 1)[1].strip() for l in open("/proc/cpuinfo") if l.startswith("model name")][0]
+    except Exception:
+        pass
+    probe = cpu_sample(fb, 2e8)
+    rate = probe.n_cells / max(run_cpu(probe, "reference"), 1e-6)
+    cores = os.cpu_count() or 1
+    for isa, isa_name in ((2, "avx512"), (1, "avx256")):
+        for ftz in (0, 1):
+            for nt in (cores, 1):
+                sample = cpu_sample(fb, rate * seconds * nt / cores)
+                t = time.perf_counter()
+                r = oracle.run_ref(sample, nthreads=nt, isa=isa, ftz=ftz)
+                dt = time.perf_counter() - t
+                out["variants"].append({"isa": isa_name, "ftz": bool(ftz), "threads": nt, "gcups": sample.n_cells / dt / 1e9,
+                                        "cells": sample.n_cells, "rescued_frac": float(r.rescued.mean())})
+    return out
+
+
 def cpu_baseline(fb, seconds=12.0):
     import oracle
     oracle.build()
@@ -160,7 +184,14 @@ def cpu_baseline(fb, seconds=12.0):
     rate = probe.n_cells / max(dt, 1e-6)
     sample = cpu_sample(fb, rate * seconds)
     dt = run_cpu(sample, kind)
-    return {"value": sample.n_cells / dt / 1e9, "unit": UNIT, "cores": cores, "kind": kind,
+    ftz_on = None
+    if kind == "reference":
+        # the same code with x86 flush-to-zero on, as GKL's JNI entry sets it (IntelPairHmm.cc:66-70): the
+        # benchmark's C entry leaves it off and pays for denormals in the FP32 pass
+        t = time.perf_counter()
+        oracle.run_ref(sample, nthreads=0, ftz=1)
+        ftz_on = sample.n_cells / (time.perf_counter() - t) / 1e9
+    return {"value": sample.n_cells / dt / 1e9, "unit": UNIT, "cores": cores, "kind": kind, "value_ftz_on": ftz_on,
             "sample": "first %d batches of the workload: %d pairs, %.3e cells, %.1f s; %s, OpenMP schedule(dynamic,1) over "
                       "pairs as IntelPairHmmCSource.cpp:64-66, FTZ off as the benchmark ships" % (
                           sample.n_batches, sample.n_pairs, sample.n_cells, dt,
@@ -216,6 +247,8 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--kernel", default=os.environ.get("PHMM_BENCH_KERNEL", "fast"), choices=["exact", "fast"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-variants", action="store_true",
+                    help="add the reference's AVX-512 / AVX-256 x FTZ off / on x all threads / 1 thread table to cpu_baseline")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -340,6 +373,8 @@ def main():
         }
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(fb)
+            if args.cpu_variants and line["cpu_baseline"]["kind"] == "reference":
+                line["cpu_baseline"].update(cpu_variants(fb))
         print(json.dumps(line))
     eng.close()
     if world > 1:
