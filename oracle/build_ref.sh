@@ -62,3 +62,20 @@ g++ $SWF -c "$HERE/sw_ref_harness.cpp" -o "$obj/sw_ref_harness.o"
 g++ -shared -fopenmp -Wl,-Bsymbolic -o "$OUT/libsw_ref.so" "$obj"/*.o
 rm -rf "$obj"
 echo "built $OUT/libsw_ref.so"
+
+# ---- the reference's own runnable driver, UNMODIFIED, linked once against the reference objects and once
+# against libphmm_cuda.so (the link-time drop-in of INTEGRATION.md section 1).  benchmarks/phmm's drivers need
+# PALISADE headers; tools/GKL/src/examples/PairHMM/PairHMMUnitTest.cpp is the same parser and the same
+# computelikelihoodsboth call without them (SURVEY.md 8c "Drivers").
+EX="$REF/tools/GKL/src/examples/PairHMM"
+PKG="$(cd "$HERE/.." && pwd)/genomicsbench_palisade_b200"
+if [ -f "$EX/PairHMMUnitTest.cpp" ]; then
+  g++ -O2 -std=c++11 -fopenmp -w -I"$EX" "$EX/PairHMMUnitTest.cpp" -o "$OUT/gkl_example_driver_ref" \
+      -L"$OUT" -lphmm_ref -Wl,-rpath,'$ORIGIN'
+  echo "built $OUT/gkl_example_driver_ref"
+  if [ -f "$PKG/libphmm_cuda.so" ]; then
+    g++ -O2 -std=c++11 -fopenmp -w -I"$EX" "$EX/PairHMMUnitTest.cpp" -o "$OUT/gkl_example_driver_cuda" \
+        -L"$PKG" -lphmm_cuda -Wl,-rpath,'$ORIGIN/../../genomicsbench_palisade_b200'
+    echo "built $OUT/gkl_example_driver_cuda"
+  fi
+fi

@@ -328,6 +328,43 @@ def test_driver_cli_with_binary_cache(tmp_path):
     assert np.array_equal(outs[0][0], outs[2][0])
 
 
+def test_unmodified_reference_driver_linked_against_libphmm_cuda(tmp_path):
+    """INTEGRATION.md section 1 for real: the reference's own driver source
+    (tools/GKL/src/examples/PairHMM/PairHMMUnitTest.cpp, compiled unmodified by oracle/build_ref.sh in the
+    build container) linked against libphmm_cuda.so prints the likelihoods its twin linked against the
+    reference's own objects prints."""
+    import os
+    import subprocess
+    from conftest import ROOT
+    cuda = os.path.join(ROOT, "oracle", "_ref", "gkl_example_driver_cuda")
+    ref = os.path.join(ROOT, "oracle", "_ref", "gkl_example_driver_ref")
+    if not (os.path.exists(cuda) and os.path.exists(ref)):
+        pytest.skip("driver binaries are built only where /root/reference exists")
+    fb = synth.generic(17, 5, (2, 10), (1, 6), (20, 200), (30, 400), q_rng=(6, 45), foreign_frac=0.3)
+    path = str(tmp_path / "in.txt")
+    open(path, "wb").write(fb.to_text())
+    outs = []
+    for exe in (cuda, ref):
+        pr = subprocess.run([exe, path], capture_output=True, text=True, timeout=300,
+                            env=dict(os.environ, CHECK="1", OMP_NUM_THREADS="4"))
+        assert pr.returncode == 0 and "PairHMM completed." in pr.stdout, pr.stderr
+        vals = []
+        for ln in pr.stdout.split("\n"):
+            try:
+                vals.append(float(ln))          # "%lf" lines of check_results (:158-161); the fork's own
+            except ValueError:                  # "i: .. result_final" chatter and headers are skipped
+                pass
+        outs.append(np.array(vals))
+    assert len(outs[0]) == len(outs[1]) == fb.n_pairs
+    # default = bit-exact kernels: the FP32 / FP64 sums are identical; the printed value goes through
+    # log10f / log10 (IntelPairHmmCSource.cpp:75,78), CUDA's on one side and glibc's on the other, which
+    # differ in the last float bit now and then.  log10f(sum) lies in [8, 36.2) before the float subtraction
+    # of log10f(2^120) (:78), so one ulp there is 3.8e-6: two of them + the "%lf" rounding, far inside 1e-4
+    tol = 2 * 2.0 ** -18 + 1.1e-6 + 3 * 2.0 ** -23 * np.abs(outs[1])
+    assert np.all(np.abs(outs[0] - outs[1]) <= tol), np.max(np.abs(outs[0] - outs[1]))
+    assert np.all(np.abs(outs[0] - oracle.run_port(fb).out) <= tol)
+
+
 def test_full_size_properties():
     """BASELINE config 2 at full size (2 M pairs): size-independent checks instead of the oracle."""
     fb = synth.c2_large()
