@@ -5,8 +5,12 @@
 // all haplotypes of an active region, results read-major (JavaData.h:44-68), FP32 with FP64 rescue
 // or -- with use_double -- FP64 for every pair (:123-124).  Host-only translation unit: the work
 // is done by phmm_compute_flat.
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "phmm_host.h"
@@ -17,6 +21,7 @@ struct phmm_gatk {
     std::string error;
     // scratch reused across calls (GATK calls once per active region, tens of thousands of times)
     phmm::ParsedBatches b;
+    int64_t read_bytes = 0;          // extent of the read pools in use by the current call
     std::vector<double> out;
 };
 
@@ -27,45 +32,75 @@ void clear(phmm::ParsedBatches &b)
 {
     b.batch_num_reads.clear(); b.batch_num_haps.clear();
     b.read_len.clear(); b.read_off.clear(); b.hap_len.clear(); b.hap_off.clear();
-    b.rs.clear(); b.q.clear(); b.i.clear(); b.d.clear(); b.c.clear(); b.hap.clear();
+    // the byte pools keep their size: they are overwritten up to the new extent, and growing a vector
+    // value-initialises (memsets) the new part -- a second pass over tens of megabytes per call
 }
 
-int append_region(phmm_gatk *g, const phmm_gatk_read *reads, int32_t n_reads, const phmm_gatk_hap *haps,
-                  int32_t n_haps)
+// Validates the regions and lays out the tables; the bytes are copied afterwards, one host thread per pool.
+int layout_regions(phmm_gatk *g, const phmm_gatk_region *regions, int64_t n_regions, int64_t *npairs)
 {
     phmm::ParsedBatches &b = g->b;
-    if (n_reads < 0 || n_haps < 0 || (n_reads && !reads) || (n_haps && !haps)) {
-        g->error = "negative count or NULL array";
-        return PHMM_ERR_ARG;
-    }
-    b.batch_num_reads.push_back(n_reads);
-    b.batch_num_haps.push_back(n_haps);
-    for (int32_t r = 0; r < n_reads; ++r) {
-        const phmm_gatk_read &rd = reads[r];
-        if (rd.length <= 0) { g->error = "readBases of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
-        if (rd.length > PHMM_MAX_SEQ_LEN) { g->error = "read longer than PHMM_MAX_SEQ_LEN"; return PHMM_ERR_TOO_LONG; }
-        if (!rd.readBases || !rd.readQuals || !rd.insertionGOP || !rd.deletionGOP || !rd.overallGCP) {
-            g->error = "NULL field in ReadDataHolder";
+    int64_t rbytes = 0, hbytes = 0;
+    *npairs = 0;
+    for (int64_t k = 0; k < n_regions; ++k) {
+        const phmm_gatk_region &rg = regions[k];
+        if (rg.n_reads < 0 || rg.n_haps < 0 || (rg.n_reads && !rg.reads) || (rg.n_haps && !rg.haps)) {
+            g->error = "negative count or NULL array";
             return PHMM_ERR_ARG;
         }
-        b.read_len.push_back(rd.length);
-        b.read_off.push_back((int64_t)b.rs.size());
-        b.rs.insert(b.rs.end(), rd.readBases, rd.readBases + rd.length);
-        b.q.insert(b.q.end(), rd.readQuals, rd.readQuals + rd.length);
-        b.i.insert(b.i.end(), rd.insertionGOP, rd.insertionGOP + rd.length);
-        b.d.insert(b.d.end(), rd.deletionGOP, rd.deletionGOP + rd.length);
-        b.c.insert(b.c.end(), rd.overallGCP, rd.overallGCP + rd.length);
+        b.batch_num_reads.push_back(rg.n_reads);
+        b.batch_num_haps.push_back(rg.n_haps);
+        for (int32_t r = 0; r < rg.n_reads; ++r) {
+            const phmm_gatk_read &rd = rg.reads[r];
+            if (rd.length <= 0) { g->error = "readBases of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+            if (rd.length > PHMM_MAX_SEQ_LEN) { g->error = "read longer than PHMM_MAX_SEQ_LEN"; return PHMM_ERR_TOO_LONG; }
+            if (!rd.readBases || !rd.readQuals || !rd.insertionGOP || !rd.deletionGOP || !rd.overallGCP) {
+                g->error = "NULL field in ReadDataHolder";
+                return PHMM_ERR_ARG;
+            }
+            b.read_len.push_back(rd.length);
+            b.read_off.push_back(rbytes);
+            rbytes += rd.length;
+        }
+        for (int32_t h = 0; h < rg.n_haps; ++h) {
+            const phmm_gatk_hap &hp = rg.haps[h];
+            if (hp.length <= 0) { g->error = "haplotypeBases of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+            if (hp.length > PHMM_MAX_SEQ_LEN) { g->error = "haplotype longer than PHMM_MAX_SEQ_LEN"; return PHMM_ERR_TOO_LONG; }
+            if (!hp.haplotypeBases) { g->error = "NULL haplotypeBases"; return PHMM_ERR_ARG; }
+            b.hap_len.push_back(hp.length);
+            b.hap_off.push_back(hbytes);
+            hbytes += hp.length;
+        }
+        const int64_t n = (int64_t)rg.n_reads * rg.n_haps;
+        if (n && !rg.likelihoods) { g->error = "NULL likelihoods"; return PHMM_ERR_ARG; }
+        *npairs += n;
     }
-    for (int32_t h = 0; h < n_haps; ++h) {
-        const phmm_gatk_hap &hp = haps[h];
-        if (hp.length <= 0) { g->error = "haplotypeBases of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
-        if (hp.length > PHMM_MAX_SEQ_LEN) { g->error = "haplotype longer than PHMM_MAX_SEQ_LEN"; return PHMM_ERR_TOO_LONG; }
-        if (!hp.haplotypeBases) { g->error = "NULL haplotypeBases"; return PHMM_ERR_ARG; }
-        b.hap_len.push_back(hp.length);
-        b.hap_off.push_back((int64_t)b.hap.size());
-        b.hap.insert(b.hap.end(), hp.haplotypeBases, hp.haplotypeBases + hp.length);
-    }
+    for (std::vector<uint8_t> *v : {&b.rs, &b.q, &b.i, &b.d, &b.c})
+        if (v->size() < (size_t)rbytes) v->resize((size_t)rbytes + (size_t)rbytes / 4);
+    if (b.hap.size() < (size_t)hbytes) b.hap.resize((size_t)hbytes + (size_t)hbytes / 4);
+    g->read_bytes = rbytes;
     return PHMM_OK;
+}
+
+void copy_pool(phmm_gatk *g, const phmm_gatk_region *regions, int64_t n_regions, int which)
+{
+    phmm::ParsedBatches &b = g->b;
+    uint8_t *dst = which == 0 ? b.rs.data() : which == 1 ? b.q.data() : which == 2 ? b.i.data()
+                 : which == 3 ? b.d.data() : which == 4 ? b.c.data() : b.hap.data();
+    for (int64_t k = 0; k < n_regions; ++k) {
+        const phmm_gatk_region &rg = regions[k];
+        if (which == 5) {
+            for (int32_t h = 0; h < rg.n_haps; ++h) { memcpy(dst, rg.haps[h].haplotypeBases, (size_t)rg.haps[h].length); dst += rg.haps[h].length; }
+            continue;
+        }
+        for (int32_t r = 0; r < rg.n_reads; ++r) {
+            const phmm_gatk_read &rd = rg.reads[r];
+            const uint8_t *src = which == 0 ? rd.readBases : which == 1 ? rd.readQuals : which == 2 ? rd.insertionGOP
+                               : which == 3 ? rd.deletionGOP : rd.overallGCP;
+            memcpy(dst, src, (size_t)rd.length);
+            dst += rd.length;
+        }
+    }
 }
 }  // namespace
 
@@ -103,18 +138,29 @@ extern "C" int phmm_gatk_init(int device, int use_double, int max_threads, int u
 extern "C" int phmm_gatk_compute_regions(phmm_gatk *g, const phmm_gatk_region *regions, int64_t n_regions)
 {
     if (!g || n_regions < 0 || (n_regions && !regions)) return PHMM_ERR_ARG;
+    static const bool trace = getenv("PHMM_TRACE") != nullptr;
+    struct timespec ts0, ts1;
+    clock_gettime(CLOCK_MONOTONIC, &ts0);
     clear(g->b);
     int64_t npairs = 0;
-    for (int64_t k = 0; k < n_regions; ++k) {
-        const phmm_gatk_region &rg = regions[k];
-        int rc = append_region(g, rg.reads, rg.n_reads, rg.haps, rg.n_haps);
-        if (rc != PHMM_OK) return rc;
-        const int64_t n = (int64_t)rg.n_reads * rg.n_haps;
-        if (n && !rg.likelihoods) { g->error = "NULL likelihoods"; return PHMM_ERR_ARG; }
-        npairs += n;
+    int rc0 = layout_regions(g, regions, n_regions, &npairs);
+    if (rc0 != PHMM_OK) return rc0;
+    if (g->read_bytes > (1 << 20)) {
+        // many regions: the staging copy is memory-bound host work, one thread per pool
+        std::thread th[5];
+        for (int w = 0; w < 5; ++w) th[w] = std::thread(copy_pool, g, regions, n_regions, w + 1);
+        copy_pool(g, regions, n_regions, 0);
+        for (int w = 0; w < 5; ++w) th[w].join();
+    } else {
+        for (int w = 0; w < 6; ++w) copy_pool(g, regions, n_regions, w);
     }
     if (npairs == 0) return PHMM_OK;
     g->b.finish();
+    if (trace) {
+        clock_gettime(CLOCK_MONOTONIC, &ts1);
+        fprintf(stderr, "phmm trace: gatk staging of %lld regions, %zu read bytes x 5: %.2f ms\n", (long long)n_regions,
+                (size_t)g->read_bytes, (ts1.tv_sec - ts0.tv_sec) * 1e3 + (ts1.tv_nsec - ts0.tv_nsec) * 1e-6);
+    }
     double *dst = g->out.data();
     if (n_regions == 1) {
         dst = regions[0].likelihoods;          // straight into the caller's array
