@@ -7,7 +7,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -387,7 +389,9 @@ extern "C" int phmm_workload_destroy(phmm_workload *w)
 // Plans `fb`, places the workload's buffers (in `arena` when given, which must be idle; else in one
 // cudaMalloc) and queues the uploads on `up`.  Does not wait for them: the caller orders later work
 // behind an event on `up`, or synchronises.
-static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, cudaStream_t up, phmm_workload **out)
+// `prebuilt`: a plan of `fb` made ahead of time (the planner thread of phmm_compute_flat); it is moved from.
+static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, cudaStream_t up, phmm_workload **out,
+                     Plan *prebuilt = nullptr)
 {
     *out = nullptr;
     phmm_workload *w = new phmm_workload();
@@ -395,7 +399,9 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     w->precision = ctx->precision;
     w->arena = arena;
     std::string err;
-    int rc = build_plan(*fb, plan_options(ctx), &w->plan, &err);
+    int rc = PHMM_OK;
+    if (prebuilt) w->plan = std::move(*prebuilt);
+    else rc = build_plan(*fb, plan_options(ctx), &w->plan, &err);
     if (rc != PHMM_OK) { ctx->error = err; delete w; return rc; }
     Plan &P = w->plan;
     w->n_pairs = P.n_pairs;
@@ -859,16 +865,47 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         wl[slot] = nullptr;
         return PHMM_OK;
     };
+    // A planner thread runs ahead of the loop below: with many small batches (active regions) planning a
+    // chunk takes as long as its kernels, and the loop's own time is better spent on uploads and launches.
+    struct PlanJob { Plan plan; std::string err; int rc = PHMM_OK; bool done = false; };
+    std::vector<PlanJob> jobs(chunks.size());
+    std::mutex pmu;
+    std::condition_variable pcv;
+    bool pstop = false;
+    const PlanOptions popt = plan_options(ctx);
+    std::thread planner;
+    if (chunks.size() > 1)
+        planner = std::thread([&]() {
+            for (size_t j = 0; j < chunks.size(); ++j) {
+                { std::lock_guard<std::mutex> lk(pmu); if (pstop) return; }
+                const phmm_flat_batches sub = sub_batches(fb, chunks[j]);
+                const int prc = build_plan(sub, popt, &jobs[j].plan, &jobs[j].err);
+                { std::lock_guard<std::mutex> lk(pmu); jobs[j].rc = prc; jobs[j].done = true; }
+                pcv.notify_all();
+                if (prc != PHMM_OK) return;
+            }
+        });
+    struct PlannerGuard {
+        std::thread &t; std::mutex &m; bool &stop;
+        ~PlannerGuard() { { std::lock_guard<std::mutex> lk(m); stop = true; } if (t.joinable()) t.join(); }
+    } planner_guard{planner, pmu, pstop};
     for (size_t j = 0; j < chunks.size() && rc == PHMM_OK; ++j) {
         const int slot = (int)(j % phmm_ctx::N_SLOTS);
         // the slot's arena must be idle: wait for the chunk that used it and fetch its results
         if (wl[slot]) rc = retire(j - phmm_ctx::N_SLOTS);
         if (rc != PHMM_OK) break;
+        Plan *prebuilt = nullptr;
+        if (planner.joinable()) {
+            std::unique_lock<std::mutex> lk(pmu);
+            pcv.wait(lk, [&]() { return jobs[j].done; });
+            if (jobs[j].rc != PHMM_OK) { ctx->error = jobs[j].err; rc = jobs[j].rc; break; }
+            prebuilt = &jobs[j].plan;
+        }
         const Chunk &c = chunks[j];
         phmm_flat_batches sub = sub_batches(fb, c);
         StreamSet &ss = ctx->ss[slot];
         const double tc0 = wall_ms();
-        rc = wl_create(ctx, &sub, &ctx->arena[slot], ctx->copy_in, &wl[slot]);
+        rc = wl_create(ctx, &sub, &ctx->arena[slot], ctx->copy_in, &wl[slot], prebuilt);
         if (rc != PHMM_OK) break;
         const double tc1 = wall_ms();
         if (cudaEventRecord(ss.ev_uploaded, ctx->copy_in) != cudaSuccess) { ctx->error = "cudaEventRecord failed"; rc = PHMM_ERR_CUDA; break; }
