@@ -569,11 +569,14 @@ phmm_forward_kernel(const KernelParams<T> P)
     }
 }
 
+#ifndef PHMM_F64_MINB3
+#define PHMM_F64_MINB3 7
+#endif
 // Minimum resident groups of four warps per SM requested from ptxas (caps registers per thread).
 template <typename T, int KH>
 struct MinBlocks {
     static constexpr int K = KH * (sizeof(T) / 4);
-    static constexpr int value = K <= 2 ? 6 : K <= 4 ? 4 : K <= 6 ? 3 : 2;
+    static constexpr int value = K <= 2 ? 6 : K <= 4 ? 4 : K <= 6 ? 3 : (sizeof(T) == 8 && KH <= PHMM_F64_MINB3) ? 3 : 2;
 };
 
 typedef void (*KernelF32)(const KernelParams<float>);
