@@ -21,22 +21,35 @@ const int N_CLASSES = 12;                      // rows per lane; the last class 
 const int CLASS_KH[N_CLASSES] = {1, 2, 3, 4, 6, 8, 10, 12, 16, 20, 24, 32};
 
 typedef void (*Kernel)(const Params);
-Kernel kernel_for(int c)
+template <bool CUT>
+Kernel kernel_of(int c)
 {
     switch (c) {
-    case 0: return sw_align_kernel<1>;
-    case 1: return sw_align_kernel<2>;
-    case 2: return sw_align_kernel<3>;
-    case 3: return sw_align_kernel<4>;
-    case 4: return sw_align_kernel<6>;
-    case 5: return sw_align_kernel<8>;
-    case 6: return sw_align_kernel<10>;
-    case 7: return sw_align_kernel<12>;
-    case 8: return sw_align_kernel<16>;
-    case 9: return sw_align_kernel<20>;
-    case 10: return sw_align_kernel<24>;
-    default: return sw_align_kernel<32>;
+    case 0: return sw_align_kernel<1, CUT>;
+    case 1: return sw_align_kernel<2, CUT>;
+    case 2: return sw_align_kernel<3, CUT>;
+    case 3: return sw_align_kernel<4, CUT>;
+    case 4: return sw_align_kernel<6, CUT>;
+    case 5: return sw_align_kernel<8, CUT>;
+    case 6: return sw_align_kernel<10, CUT>;
+    case 7: return sw_align_kernel<12, CUT>;
+    case 8: return sw_align_kernel<16, CUT>;
+    case 9: return sw_align_kernel<20, CUT>;
+    case 10: return sw_align_kernel<24, CUT>;
+    default: return sw_align_kernel<32, CUT>;
     }
+}
+Kernel kernel_for(int c, bool cut) { return cut ? kernel_of<true>(c) : kernel_of<false>(c); }
+
+// The diagonal term max(H(i-1, j-1) + w, MATRIX_MIN_CUTOFF) (PairWiseSW.h:5-7) can only be clamped when some H
+// falls below -1e8.  H(i, j) >= H(i-1, j-1) + min(match, mismatch), and the boundary values are 0 or
+// open + (k - 1) * extend, so with MAX_LEN rows and columns this bound keeps every H above the cutoff and the
+// kernels without the clamp give the same bits.
+bool cutoff_can_bind(const sw_params *pm)
+{
+    const int64_t w = std::min<int64_t>(std::min(pm->match, pm->mismatch), 0);
+    const int64_t lo = -(std::llabs((long long)pm->open) + (int64_t)(MAX_LEN - 1) * std::llabs((long long)pm->extend)) + (int64_t)MAX_LEN * w;
+    return lo - 1 <= (int64_t)SW_MIN_CUTOFF;
 }
 }  // namespace
 
@@ -69,7 +82,8 @@ struct sw_workload {
     int32_t cigar_stride = 0;
     int32_t class_ntasks[N_CLASSES] = {0};
     int64_t class_off[N_CLASSES] = {0};
-    int64_t class_bt_stride[N_CLASSES] = {0};
+    int64_t class_bt_stride[N_CLASSES] = {0};      // words per warp: last-row scratch + backtrack words
+    int32_t class_lr_words[N_CLASSES] = {0};
     int class_grid[N_CLASSES] = {0};
     int64_t class_bt_off[N_CLASSES] = {0}, class_elems_off[N_CLASSES] = {0};   // own scratch: classes run concurrently
     int32_t elems_stride = 0;
@@ -140,9 +154,10 @@ extern "C" int sw_create(int device, sw_ctx **out)
     }
     const int smem = WARPS_PER_BLOCK * (int)sizeof(WarpSmem);
     for (int c = 0; c < N_CLASSES; ++c) {
-        Kernel k = kernel_for(c);
-        if ((e = cudaFuncSetAttribute((const void *)k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess)
-            return bail("cudaFuncSetAttribute", e);
+        Kernel k = kernel_for(c, false);
+        for (Kernel kk : {k, kernel_for(c, true)})
+            if ((e = cudaFuncSetAttribute((const void *)kk, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess)
+                return bail("cudaFuncSetAttribute", e);
         int nb = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void *)k, WARPS_PER_BLOCK * 32, smem) != cudaSuccess || nb < 1) nb = 1;
         ctx->blocks_per_sm[c] = nb;
@@ -242,6 +257,7 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
         max_sum = std::max(max_sum, l1 + l2);
         const int kh = CLASS_KH[c], nw = (kh + 7) / 8;
         w->class_bt_stride[c] = std::max<int64_t>(w->class_bt_stride[c], (int64_t)(l2 + 31) * nw * 32);
+        w->class_lr_words[c] = std::max<int32_t>(w->class_lr_words[c], ((l2 + 1) * ((kh + 3) & ~3) + 31) & ~31);
         w->bt_bytes += (int64_t)l2 * ((l1 + kh - 1) / kh) * nw * 4;        // one word per active lane, word slot and step
     }
     w->elems_stride = max_sum + 8;
@@ -260,6 +276,7 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
         w->class_grid[c] = (int)std::max<int64_t>(1, std::min(full, want));
         const int64_t warps = (int64_t)w->class_grid[c] * WARPS_PER_BLOCK;
         if (recs[c].empty()) continue;
+        w->class_bt_stride[c] += w->class_lr_words[c];
         w->class_bt_off[c] = bt_words;
         w->class_elems_off[c] = warps_sum * w->elems_stride;
         bt_words += warps * w->class_bt_stride[c];
@@ -326,6 +343,7 @@ static int wl_launch(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strat
     SW_TRY(ctx, cudaEventRecord(sl.ev_fork, st));
     for (int k = 0; k < Slot::N_SIDE; ++k) SW_TRY(ctx, cudaStreamWaitEvent(sl.side[k], sl.ev_fork, 0));
     w->launches = 0;
+    const bool cut = cutoff_can_bind(pm);
     // longest-running class first: its tail is covered by the blocks of the next
     for (int c = N_CLASSES - 1; c >= 0; --c) {
         if (w->class_ntasks[c] == 0) continue;
@@ -338,11 +356,11 @@ static int wl_launch(sw_ctx *ctx, sw_workload *w, const sw_params *pm, int strat
         P.match = pm->match; P.mismatch = pm->mismatch; P.open = pm->open; P.extend = pm->extend;
         P.strategy = strategy;
         P.one = 1;
-        P.bt = w->d_bt + w->class_bt_off[c]; P.bt_stride = w->class_bt_stride[c];
+        P.bt = w->d_bt + w->class_bt_off[c]; P.bt_stride = w->class_bt_stride[c]; P.lr_words = w->class_lr_words[c];
         P.elems = w->d_elems + w->class_elems_off[c]; P.elems_stride = w->elems_stride;
         P.score = w->d_score; P.offset = w->d_offset; P.cigar_len = w->d_cigar_len;
         P.cigar = w->d_cigar; P.cigar_stride = w->cigar_stride;
-        kernel_for(c)<<<w->class_grid[c], WARPS_PER_BLOCK * 32, WARPS_PER_BLOCK * sizeof(WarpSmem), sl.side[w->launches % Slot::N_SIDE]>>>(P);
+        kernel_for(c, cut)<<<w->class_grid[c], WARPS_PER_BLOCK * 32, WARPS_PER_BLOCK * sizeof(WarpSmem), sl.side[w->launches % Slot::N_SIDE]>>>(P);
         SW_TRY(ctx, cudaGetLastError());
         ++w->launches;
     }

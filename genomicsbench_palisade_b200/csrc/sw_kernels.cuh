@@ -13,9 +13,13 @@
 //   * Backtrack: 4 bits per cell (MATCH/INSERT/DELETE + the two *_EXT flags, :21-25), eight cells of
 //     a lane per 32-bit word, stored at [step][word][lane] -- coalesced 128-byte lines per warp and
 //     step.  The reference writes 16 bits per cell (:170).
-//   * Last row / last column scores go to shared memory; the best cell is chosen afterwards in the
-//     reference's visiting order (:209-236): a warp-wide maximum, then the tie rule applied to the
-//     cells that reach it, in anti-diagonal order.
+//   * Last column scores go to shared memory.  The last row sits in a register slot that depends on
+//     the pair (row nrow of lane (nrow - 1) / KH): picking it per cell would cost a compare and a
+//     select on the ALU pipe, the pipe that bounds the kernel, so that lane stores all its KH row
+//     values of the step with 128-bit stores into per-warp scratch in L2 and the scan reads the one
+//     column it needs.  The best cell is chosen afterwards in the reference's visiting order
+//     (:209-236): a warp-wide maximum, then the tie rule applied to the cells that reach it, in
+//     anti-diagonal order.
 //   * Traceback and CIGAR formatting (:265-412) by the warp on the backtrack words it just wrote,
 //     through a 32-step window of words fetched with one warp-wide load.
 #ifndef SW_KERNELS_CUH
@@ -60,8 +64,9 @@ struct Params {
     int32_t *counter;           // queue head
     int32_t match, mismatch, open, extend, strategy;
     int32_t one;                // = 1, opaque to the compiler: see fma_add()
-    uint32_t *bt;               // per-warp backtrack scratch
-    int64_t bt_stride;          // words per warp
+    uint32_t *bt;               // per-warp scratch: lr_words of last-row values, then the backtrack words
+    int64_t bt_stride;          // words per warp (both parts)
+    int32_t lr_words;           // multiple of 32
     int2 *elems;                // per-warp CIGAR element scratch
     int32_t elems_stride;
     int32_t *score, *offset, *cigar_len;
@@ -69,9 +74,9 @@ struct Params {
     int32_t cigar_stride;
 };
 
-// per-warp shared memory: last row, last column, alt bytes
+// per-warp shared memory: last column, alt bytes
 struct __align__(16) WarpSmem {
-    int32_t lastrow[MAX_LEN + 1], lastcol[MAX_LEN + 1];
+    int32_t lastcol[MAX_LEN + 1];
     uint8_t alt[MAX_LEN + 16];
 };
 
@@ -114,19 +119,40 @@ __device__ __forceinline__ void bt_flags(uint32_t &word, int32_t one, int32_t e1
           "n"((uint32_t)OP_DELETE << SHIFT), "n"((uint32_t)OP_INSERT << SHIFT));
 }
 
+// Hd + (c1 == c2 ? match : mismatch) without the select and without the MATRIX_MIN_CUTOFF clamp
+// (PairWiseSW.h:5-7): one compare on the ALU pipe, two IMADs on the FMA pipe.  Only for parameters
+// under which the clamp can never bind (sw_api.cu: cutoff_can_bind).
+__device__ __forceinline__ int32_t diag_score(int32_t hd, uint32_t c1, uint32_t c2, int32_t one, int32_t match, int32_t mismatch)
+{
+    int32_t r;
+    asm("{\n\t"
+        ".reg .pred pe;\n\t"
+        "setp.eq.u32 pe, %2, %3;\n\t"
+        "mad.lo.s32 %0, %1, %4, %6;\n\t"
+        "@pe mad.lo.s32 %0, %1, %4, %5;\n\t"
+        "}"
+        : "=&r"(r)
+        : "r"(hd), "r"(c1), "r"(c2), "r"(one), "r"(match), "r"(mismatch));
+    return r;
+}
+
 // KH rows per lane; a pair runs in the smallest class with 32 * KH >= len1, so one stripe of the
 // wavefront always covers the whole matrix (MAX_LEN = 32 * 32) and most lanes hold real rows.
-template <int KH>
+// CUT: keep the MATRIX_MIN_CUTOFF clamp of the diagonal term (parameters large enough for it to bind).
+template <int KH, bool CUT>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 sw_align_kernel(const Params P)
 {
     static_assert(KH >= 1 && KH <= 32, "one stripe must cover MAX_LEN rows");
     constexpr int NW = (KH + 7) / 8;                     // backtrack words per lane and step
+    constexpr int KH4 = (KH + 3) & ~3;                   // last-row scratch: KH4 values per column
     extern __shared__ __align__(16) uint8_t smem_raw[];
     WarpSmem &S = reinterpret_cast<WarpSmem *>(smem_raw)[threadIdx.x >> 5];
     const int lane = threadIdx.x & 31;
     const int warp_global = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
-    uint32_t *bt = P.bt + (int64_t)warp_global * P.bt_stride;
+    int32_t *lr = reinterpret_cast<int32_t *>(P.bt + (int64_t)warp_global * P.bt_stride);
+    uint32_t *bt = P.bt + (int64_t)warp_global * P.bt_stride + P.lr_words;
+    const bool row_cands = (P.strategy == ST_SOFTCLIP || P.strategy == ST_IGNORE);
     int2 *elems = P.elems + (int64_t)warp_global * P.elems_stride;
     const bool lead = (P.strategy == ST_INDEL || P.strategy == ST_LEADING_INDEL);
 
@@ -157,8 +183,7 @@ sw_align_kernel(const Params P)
             // H(i0 - 1, 0): diagonal neighbour of the lane's first row at column 1
             int32_t Hd_next = (lane == 0) ? 0 : (lead ? P.open + (i0 - 2) * P.extend : 0);
             int32_t Hbot = 0, Fbot = SW_LOW_INIT;
-            const int pr_row = (nrow - 1) % KH;          // register slot of row nrow in its lane
-            const int lr_lane = (nrow - 1) / KH;
+            const bool lr_store = row_cands && lane == (nrow - 1) / KH;      // last-row candidates: SOFTCLIP / IGNORE only
             const int steps = ncol + lanes_used - 1;
             for (int st = 0; st < steps; ++st) {
                 const int j = st - lane + 1;             // this lane's column (1-based)
@@ -172,7 +197,6 @@ sw_align_kernel(const Params P)
                     uint32_t word[NW];
 #pragma unroll
                     for (int q = 0; q < NW; ++q) word[q] = 0;
-                    int32_t hsel = 0;
                     static_for<KH>([&](auto pc) {
                         constexpr int p = decltype(pc)::value;
                         // MAIN_CODE (:3-37); max(a + b, c) is one VIADDMNMX
@@ -180,19 +204,25 @@ sw_align_kernel(const Params P)
                         const int32_t e11 = __viaddmax_s32(Hl[p], P.open, ext_h);
                         const int32_t ext_v = fma_add(Ft, P.one, P.extend);
                         const int32_t f11 = __viaddmax_s32(Ht, P.open, ext_v);
-                        const int32_t h0 = __viaddmax_s32(Hd, (c1[p] == c2) ? P.match : P.mismatch, SW_MIN_CUTOFF);
+                        const int32_t h0 = CUT ? __viaddmax_s32(Hd, (c1[p] == c2) ? P.match : P.mismatch, SW_MIN_CUTOFF)
+                                               : diag_score(Hd, c1[p], c2, P.one, P.match, P.mismatch);
                         const int32_t h1 = max(h0, e11);
                         const int32_t h11 = max(h1, f11);
                         bt_flags<4 * (p % 8)>(word[p / 8], P.one, e11, ext_h, f11, ext_v, h0, h1);
                         Hd = Hl[p];
                         Ht = h11; Ft = f11;
                         Hl[p] = h11; E[p] = e11;
-                        if (p == pr_row) hsel = h11;
                     });
                     Hbot = Ht; Fbot = Ft;
 #pragma unroll
                     for (int q = 0; q < NW; ++q) bt[((int64_t)st * NW + q) * 32 + lane] = word[q];
-                    if (lane == lr_lane) S.lastrow[j] = hsel;
+                    if (lr_store) {
+                        int4 *dst = reinterpret_cast<int4 *>(lr + (int64_t)j * KH4);
+#pragma unroll
+                        for (int q = 0; q < KH4 / 4; ++q)
+                            dst[q] = make_int4(Hl[4 * q], Hl[min(4 * q + 1, KH - 1)], Hl[min(4 * q + 2, KH - 1)],
+                                               Hl[min(4 * q + 3, KH - 1)]);    // slots >= KH: never read
+                    }
                     if (j == ncol) {
 #pragma unroll
                         for (int p = 0; p < KH; ++p)
@@ -206,14 +236,14 @@ sw_align_kernel(const Params P)
         // ---- best last-row / last-column cell in the reference's visiting order (:209-236) ----------
         // slot 2d = (nrow, d - nrow) for d >= nrow + 1 (SOFTCLIP / IGNORE only), slot 2d + 1 = (d - ncol, ncol)
         // for d >= ncol + 1, d = 1 .. nrow + ncol
-        const bool row_cands = (P.strategy == ST_SOFTCLIP || P.strategy == ST_IGNORE);
+        const int pr_row = (nrow - 1) % KH;              // register slot of row nrow in its lane
         const int slot_lo = 2 * (min(nrow, ncol) + 1), slot_hi = 2 * (nrow + ncol) + 2;
         auto slot_score = [&](int slot, int32_t *sc) -> bool {
             const int d = slot >> 1;
             if (slot >= slot_hi) return false;
             if (slot & 1) { if (d < ncol + 1) return false; *sc = S.lastcol[d - ncol]; return true; }
             if (!row_cands || d < nrow + 1) return false;
-            *sc = S.lastrow[d - nrow];
+            *sc = __ldcg(lr + (int64_t)(d - nrow) * KH4 + pr_row);
             return true;
         };
         int32_t best = INT32_MIN;

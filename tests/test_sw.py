@@ -106,9 +106,13 @@ def test_gpu_matches_oracle_on_random_pairs():
             sw_pairs.synth(6, 60, ref_rng=(600, 1024), alts_per_ref=(2, 6), snp=0.02, indel=0.01),
             sw_pairs.synth(7, 150, ref_rng=(30, 400), snp=0.25, indel=0.08),
             sw_pairs.synth(8, 100, ref_rng=(5, 200), alphabet=b"AAAC"),          # low complexity: many ties
-            sw_pairs.full_length_cases()]
+            sw_pairs.full_length_cases(),
+            sw_pairs.from_lists([(b"A" * 1024, b"C" * 1024), (b"A" * 1023, b"C" * 1024)])]
     for ps in sets:
-        for pm in ((200, -150, -260, -11), (1, -1, -1, -1), (25, -50, -110, -6)):
+        # the last two parameter sets select the kernels that keep the MATRIX_MIN_CUTOFF clamp (sw_api.cu:
+        # cutoff_can_bind); with the last one the clamp decides cells of the all-mismatch 1024 x 1024 pair
+        for pm in ((200, -150, -260, -11), (1, -1, -1, -1), (25, -50, -110, -6), (200, -100000, -260, -11),
+                   (100, -100000, -100000, -100000)):
             for st in STRATEGIES:
                 ref = osw.run_port(ps, pm, st)
                 got = eng.align_pairs(ps, pm, st)
