@@ -74,9 +74,9 @@ struct Params {
     int32_t cigar_stride;
 };
 
-// per-warp shared memory: last column, alt bytes
+// per-warp shared memory: last row (copied from the L2 scratch after the DP), last column, alt bytes
 struct __align__(16) WarpSmem {
-    int32_t lastcol[MAX_LEN + 1];
+    int32_t lastrow[MAX_LEN + 1], lastcol[MAX_LEN + 1];
     uint8_t alt[MAX_LEN + 16];
 };
 
@@ -236,14 +236,19 @@ sw_align_kernel(const Params P)
         // ---- best last-row / last-column cell in the reference's visiting order (:209-236) ----------
         // slot 2d = (nrow, d - nrow) for d >= nrow + 1 (SOFTCLIP / IGNORE only), slot 2d + 1 = (d - ncol, ncol)
         // for d >= ncol + 1, d = 1 .. nrow + ncol
-        const int pr_row = (nrow - 1) % KH;              // register slot of row nrow in its lane
+        if (row_cands) {
+            const int pr_row = (nrow - 1) % KH;          // register slot of row nrow in its lane
+#pragma unroll 4
+            for (int k = 1 + lane; k <= ncol; k += 32) S.lastrow[k] = __ldcg(lr + (int64_t)k * KH4 + pr_row);
+            __syncwarp();
+        }
         const int slot_lo = 2 * (min(nrow, ncol) + 1), slot_hi = 2 * (nrow + ncol) + 2;
         auto slot_score = [&](int slot, int32_t *sc) -> bool {
             const int d = slot >> 1;
             if (slot >= slot_hi) return false;
             if (slot & 1) { if (d < ncol + 1) return false; *sc = S.lastcol[d - ncol]; return true; }
             if (!row_cands || d < nrow + 1) return false;
-            *sc = __ldcg(lr + (int64_t)(d - nrow) * KH4 + pr_row);
+            *sc = S.lastrow[d - nrow];
             return true;
         };
         int32_t best = INT32_MIN;
@@ -284,20 +289,42 @@ sw_align_kernel(const Params P)
         };
         if (j < ncol) push(ST_SOFTCLIP, ncol - j);
         int state = 0;
-        // window: lane L holds the backtrack word of (w_ln, w_q) at step w_st - L, so a run of moves
-        // inside one lane's 8-row word costs one round trip to L2 instead of one per move
-        int w_ln = -1, w_q = -1, w_st = 0;
-        uint32_t wv = 0;
+        // window: lane L holds the NW backtrack words of lane w_ln at step w_st - L, so a run of moves inside
+        // one lane's rows costs one round trip to L2 (or HBM: the backtrack words of all resident warps exceed
+        // L2) instead of one per move.  A second window is fetched ahead for where a diagonal run enters the
+        // lane above (8 steps of slack for deletions on the way), so that round trip overlaps the moves.
+        int w_ln = -1, w_st = 0, n_ln = -1, n_st = 0;
+        uint32_t wv[NW], nv[NW];
+#pragma unroll
+        for (int q = 0; q < NW; ++q) wv[q] = nv[q] = 0;
         while (i > 0 && j > 0) {
             const int r = i - 1;
             const int ln = r / KH, p = r % KH, q = p / 8;
             const int st = j - 1 + ln;
-            if (ln != w_ln || q != w_q || st > w_st || st < w_st - 31) {
-                w_ln = ln; w_q = q; w_st = st;
-                const int s2 = st - lane;
-                wv = (s2 >= 0) ? __ldcg(bt + ((int64_t)s2 * NW + q) * 32 + ln) : 0u;
+            if (ln != w_ln || st > w_st || st < w_st - 31) {
+                if (ln == n_ln && st <= n_st && st >= n_st - 31) {
+                    w_st = n_st;
+#pragma unroll
+                    for (int k = 0; k < NW; ++k) wv[k] = nv[k];
+                } else {
+                    w_st = st;
+                    const int s2 = st - lane;
+#pragma unroll
+                    for (int k = 0; k < NW; ++k) wv[k] = (s2 >= 0) ? __ldcg(bt + ((int64_t)s2 * NW + k) * 32 + ln) : 0u;
+                }
+                w_ln = ln;
+                n_ln = ln - 1;
+                if (n_ln >= 0) {
+                    n_st = min(st - p - 2 + 8, ncol - 1 + n_ln);          // st of (i - p - 1, j - p - 1) in lane ln - 1, + slack
+                    const int s2 = n_st - lane;
+#pragma unroll
+                    for (int k = 0; k < NW; ++k) nv[k] = (s2 >= 0) ? __ldcg(bt + ((int64_t)s2 * NW + k) * 32 + n_ln) : 0u;
+                }
             }
-            const uint32_t w = __shfl_sync(FULL, wv, w_st - st);
+            uint32_t mine = wv[0];
+#pragma unroll
+            for (int k = 1; k < NW; ++k) if (q == k) mine = wv[k];
+            const uint32_t w = __shfl_sync(FULL, mine, w_st - st);
             const int btr = (int)((w >> (4 * (p % 8))) & 15u);
             if (state == F_INSERT_EXT) { --j; ++cur_len; state = btr & F_INSERT_EXT; }
             else if (state == F_DELETE_EXT) { --i; ++cur_len; state = btr & F_DELETE_EXT; }
