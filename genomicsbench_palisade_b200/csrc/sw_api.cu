@@ -17,26 +17,23 @@ using namespace sw;
 
 namespace {
 thread_local std::string g_create_error;
-const int N_CLASSES = 12;                      // rows per lane; the last class covers SW_MAX_SEQ_LEN = 32 * 32
-const int CLASS_KH[N_CLASSES] = {1, 2, 3, 4, 6, 8, 10, 12, 16, 20, 24, 32};
+// Rows per lane of the kernel classes.  A pair runs in the smallest class with 32 * KH >= len1; the unused
+// rows of the last lanes are issue slots spent on nothing, so up to 640 rows (where GATK's haplotypes and
+// reference windows are) every KH has its own class; the last class covers SW_MAX_SEQ_LEN = 32 * 32.
+#define SW_CLASS_LIST(X) X(0, 1) X(1, 2) X(2, 3) X(3, 4) X(4, 5) X(5, 6) X(6, 7) X(7, 8) X(8, 9) X(9, 10) X(10, 11) \
+    X(11, 12) X(12, 13) X(13, 14) X(14, 15) X(15, 16) X(16, 17) X(17, 18) X(18, 19) X(19, 20) X(20, 24) X(21, 28) X(22, 32)
+const int N_CLASSES = 23;
+#define SW_X_KH(c, kh) kh,
+const int CLASS_KH[N_CLASSES] = {SW_CLASS_LIST(SW_X_KH)};
 
 typedef void (*Kernel)(const Params);
 template <bool CUT>
 Kernel kernel_of(int c)
 {
     switch (c) {
-    case 0: return sw_align_kernel<1, CUT>;
-    case 1: return sw_align_kernel<2, CUT>;
-    case 2: return sw_align_kernel<3, CUT>;
-    case 3: return sw_align_kernel<4, CUT>;
-    case 4: return sw_align_kernel<6, CUT>;
-    case 5: return sw_align_kernel<8, CUT>;
-    case 6: return sw_align_kernel<10, CUT>;
-    case 7: return sw_align_kernel<12, CUT>;
-    case 8: return sw_align_kernel<16, CUT>;
-    case 9: return sw_align_kernel<20, CUT>;
-    case 10: return sw_align_kernel<24, CUT>;
-    default: return sw_align_kernel<32, CUT>;
+#define SW_X_CASE(c, kh) case c: return sw_align_kernel<kh, CUT>;
+        SW_CLASS_LIST(SW_X_CASE)
+    default: return nullptr;
     }
 }
 Kernel kernel_for(int c, bool cut) { return cut ? kernel_of<true>(c) : kernel_of<false>(c); }

@@ -139,8 +139,14 @@ __device__ __forceinline__ int32_t diag_score(int32_t hd, uint32_t c1, uint32_t 
 // KH rows per lane; a pair runs in the smallest class with 32 * KH >= len1, so one stripe of the
 // wavefront always covers the whole matrix (MAX_LEN = 32 * 32) and most lanes hold real rows.
 // CUT: keep the MATRIX_MIN_CUTOFF clamp of the diagonal term (parameters large enough for it to bind).
+// resident blocks per SM asked of ptxas (caps the registers at what it chose for the first version of this
+// kernel; left alone it sometimes trades a block per SM for scheduling freedom the dependency chain of a
+// cell cannot use -- measured 945 against 961 GCUPS)
+template <int KH>
+struct MinBlocks { static constexpr int value = KH <= 4 ? 8 : KH <= 8 ? 7 : KH <= 12 ? 6 : KH <= 20 ? 5 : KH <= 24 ? 4 : 3; };
+
 template <int KH, bool CUT>
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MinBlocks<KH>::value)
 sw_align_kernel(const Params P)
 {
     static_assert(KH >= 1 && KH <= 32, "one stripe must cover MAX_LEN rows");
