@@ -25,10 +25,10 @@ thread_local std::string g_create_error;
 // streams so that the tail of one persistent kernel (SMs idling while its last tasks finish) is
 // filled by the blocks of the next.
 struct StreamSet {
-    static const int N_SIDE = 4;
+    static const int N_SIDE = 8;       // 4 in use for large workloads, all for small calls (wl_launch)
     cudaStream_t main = nullptr;
-    cudaStream_t side[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
-    cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t side[N_SIDE] = {};
+    cudaEvent_t ev_fork = nullptr, ev_join[N_SIDE] = {};
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};     // timing: start, FP32 done, FP64 done
     cudaEvent_t ev_uploaded = nullptr;                     // inputs are in HBM (recorded on the upload stream)
 
@@ -64,6 +64,10 @@ struct StreamSet {
 struct Arena {
     uint8_t *base = nullptr;
     size_t cap = 0, off = 0;
+    // pinned staging for small chunks (one active region per call): every uploaded piece is laid out in it as
+    // in the arena and goes up with one copy instead of a dozen pageable ones (~8 us of driver time each)
+    uint8_t *stage = nullptr;
+    static constexpr size_t STAGE_CAP = 4u << 20;
 };
 }  // namespace
 
@@ -87,6 +91,8 @@ struct phmm_ctx {
     int64_t chunk_cells = 0;   // host-buffer entry points: cells per pipelined chunk (0 = default)
     std::string error;
     std::mutex mu;     // the legacy symbols may be entered from several OpenMP threads
+    // resident blocks per SM of each kernel (asked of the runtime once, not at every launch)
+    std::unordered_map<const void *, int> blocks_per_sm;
 };
 
 struct ClassDev {
@@ -253,6 +259,7 @@ extern "C" int phmm_destroy(phmm_ctx *ctx)
     cudaFree(ctx->d_bench);
     for (int k = 0; k < phmm_ctx::N_SLOTS; ++k) {
         cudaFree(ctx->arena[k].base);
+        if (ctx->arena[k].stage) cudaFreeHost(ctx->arena[k].stage);
         ctx->ss[k].destroy();
     }
     if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
@@ -503,31 +510,41 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     } while (0)
     const uint8_t *pools[5] = {fb->rs, fb->q, fb->i, fb->d, fb->c};
     int64_t h2d = 0;
-    for (int k = 0; k < 5; ++k)
-        for (const Plan::Segment &sg : P.segments) {
-            WL_TRY(cudaMemcpyAsync(w->d_pool + k * w->pool_stride + sg.dst, pools[k] + sg.src, (size_t)sg.len, cudaMemcpyHostToDevice, up));
-            h2d += sg.len;
-        }
-    WL_TRY(cudaMemcpyAsync(w->d_stream, P.stream.data(), P.stream.size(), cudaMemcpyHostToDevice, up));
-    WL_TRY(cudaMemcpyAsync(w->d_hap_len, P.hap_len.data(), P.hap_len.size() * sizeof(int32_t), cudaMemcpyHostToDevice, up));
-    if (!P.reads.empty())
-        WL_TRY(cudaMemcpyAsync(w->d_reads, P.reads.data(), P.reads.size() * sizeof(ReadRec), cudaMemcpyHostToDevice, up));
-    h2d += (int64_t)P.stream.size() + (int64_t)P.hap_len.size() * 4 + (int64_t)P.reads.size() * sizeof(ReadRec);
     int32_t ints[INTS_TOTAL];
     memset(ints, 0, sizeof ints);
+    for (size_t c = 0; c < P.classes.size(); ++c) ints[INTS_NTASKS + c] = w->classes[c].ntasks;
+    // everything that is uploaded sits in front of d_out: small chunks go up in one copy from pinned staging
+    const size_t upload_extent = (size_t)((uint8_t *)w->d_out - base);
+    uint8_t *stage = nullptr;
+    if (arena && upload_extent <= Arena::STAGE_CAP) {
+        if (!arena->stage && cudaMallocHost((void **)&arena->stage, Arena::STAGE_CAP) != cudaSuccess) { arena->stage = nullptr; cudaGetLastError(); }
+        stage = arena->stage;
+    }
+    // dst: device address; staged: the same offset in the staging buffer (the slot is idle: its previous chunk
+    // has been retired, so the last copy out of the buffer is complete)
+    auto put = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
+        if (bytes == 0) return cudaSuccess;
+        if (stage) { memcpy(stage + ((uint8_t *)dst - base), src, bytes); return cudaSuccess; }
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, up);
+    };
+    for (int k = 0; k < 5; ++k)
+        for (const Plan::Segment &sg : P.segments) {
+            WL_TRY(put(w->d_pool + k * w->pool_stride + sg.dst, pools[k] + sg.src, (size_t)sg.len));
+            h2d += sg.len;
+        }
+    WL_TRY(put(w->d_stream, P.stream.data(), P.stream.size()));
+    WL_TRY(put(w->d_hap_len, P.hap_len.data(), P.hap_len.size() * sizeof(int32_t)));
+    WL_TRY(put(w->d_reads, P.reads.data(), P.reads.size() * sizeof(ReadRec)));
+    h2d += (int64_t)P.stream.size() + (int64_t)P.hap_len.size() * 4 + (int64_t)P.reads.size() * sizeof(ReadRec);
     for (size_t c = 0; c < P.classes.size(); ++c) {
-        if (!P.classes[c].tasks.empty())
-            WL_TRY(cudaMemcpyAsync(w->d_tasks + w->classes[c].task_off, P.classes[c].tasks.data(),
-                                   P.classes[c].tasks.size() * sizeof(Task), cudaMemcpyHostToDevice, up));
-        if (!P.classes[c].htasks.empty())
-            WL_TRY(cudaMemcpyAsync(w->d_htasks + w->classes[c].task_off, P.classes[c].htasks.data(),
-                                   P.classes[c].htasks.size() * sizeof(HTask), cudaMemcpyHostToDevice, up));
+        WL_TRY(put(w->d_tasks + w->classes[c].task_off, P.classes[c].tasks.data(), P.classes[c].tasks.size() * sizeof(Task)));
+        WL_TRY(put(w->d_htasks + w->classes[c].task_off, P.classes[c].htasks.data(), P.classes[c].htasks.size() * sizeof(HTask)));
         h2d += (int64_t)P.classes[c].tasks.size() * sizeof(Task) + (int64_t)P.classes[c].htasks.size() * sizeof(HTask);
-        ints[INTS_NTASKS + c] = w->classes[c].ntasks;
     }
     // (copies from pageable host memory return once the source has been staged, so the plan's
     // vectors and `ints` may be released right after)
-    WL_TRY(cudaMemcpyAsync(w->d_ints, ints, sizeof ints, cudaMemcpyHostToDevice, up));
+    WL_TRY(put(w->d_ints, ints, sizeof ints));
+    if (stage) WL_TRY(cudaMemcpyAsync(base, stage, upload_extent, cudaMemcpyHostToDevice, up));
     WL_TRY(cudaMemsetAsync(w->d_raw64, 0, np * sizeof(double), up));
     WL_TRY(cudaMemsetAsync(w->d_rescued, 0, np, up));
 #undef WL_TRY
@@ -614,10 +631,16 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     // dynamic shared memory (emission table + stream ring + run table per warp) and a grid that
     // fills the device once: the kernels are persistent, warps pull tasks from the queue
     auto prepare = [&](const void *kernel, int kh, int64_t ntasks, bool longr, int *grid, int *smem, bool hp = false) -> bool {
-        *smem = WARPS_PER_BLOCK * (hp ? smem_per_warp_hp(kh) : smem_per_warp(kh));
-        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, *smem) != cudaSuccess) return false;
+        *smem = WARPS_PER_BLOCK * (hp ? smem_per_warp_hp(kh) : smem_per_warp(kh));     // a function of the kernel
         int nb = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, WARPS_PER_BLOCK * 32, *smem) != cudaSuccess || nb < 1) nb = 1;
+        auto it = ctx->blocks_per_sm.find(kernel);
+        if (it != ctx->blocks_per_sm.end()) {
+            nb = it->second;
+        } else {
+            if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, *smem) != cudaSuccess) return false;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, WARPS_PER_BLOCK * 32, *smem) != cudaSuccess || nb < 1) nb = 1;
+            ctx->blocks_per_sm[kernel] = nb;
+        }
         const int64_t full = (int64_t)nb * ctx->sm_count;
         const int64_t want = (ntasks + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
         *grid = (int)std::max<int64_t>(1, std::min(full, want));
@@ -627,14 +650,18 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     int counter_slot = 0, grid = 0, smem = 0;
     // fork: the side streams wait for everything queued on the main stream so far;
     // join: the main stream waits for the side streams that were used
+    // Large workloads: four class kernels side by side (the tail of one is filled by the blocks of the next;
+    // more of them at once only split the SMs further).  Small calls: every class kernel has a handful of
+    // tasks and lasts as long as its longest one, so all of them run at once.
+    const int n_side = P.latency ? (int)StreamSet::N_SIDE : 4;
     int n_forked = 0;
     auto fork = [&]() -> cudaError_t {
         n_forked = 0;
         return cudaEventRecord(ss.ev_fork, st);
     };
     auto side_stream = [&](cudaStream_t *out) -> cudaError_t {
-        const int k = n_forked % StreamSet::N_SIDE;
-        if (n_forked < StreamSet::N_SIDE) {
+        const int k = n_forked % n_side;
+        if (n_forked < n_side) {
             cudaError_t e = cudaStreamWaitEvent(ss.side[k], ss.ev_fork, 0);
             if (e != cudaSuccess) return e;
         }
@@ -643,7 +670,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
         return cudaSuccess;
     };
     auto join = [&]() -> cudaError_t {
-        for (int k = 0; k < std::min(n_forked, (int)StreamSet::N_SIDE); ++k) {
+        for (int k = 0; k < std::min(n_forked, n_side); ++k) {
             cudaError_t e = cudaEventRecord(ss.ev_join[k], ss.side[k]);
             if (e == cudaSuccess) e = cudaStreamWaitEvent(st, ss.ev_join[k], 0);
             if (e != cudaSuccess) return e;

@@ -32,6 +32,7 @@ struct PlanOptions {
     int resident_warps = 2368;   // warps the device keeps in flight (for adaptive run sizing)
     int force_kh = 0, force_lanes = 0;   // debugging / benchmarking: pin the kernel class
     int hp = 0;               // 1 = plan haplotype-pair tasks (fast FP32 kernels) for single-pass reads
+    int latency = -1;         // 1 = plan for the latency of a small call (32 lanes per read, one haplotype per run); -1 = decide from the size
 };
 
 struct ClassPlan {
@@ -49,6 +50,7 @@ struct Plan {
     std::vector<int32_t> hap_len;        // stream order, + 1 slack entry
     std::vector<ClassPlan> classes;
     int64_t n_pairs = 0, n_cells = 0;
+    int latency = 0;                     // planned for the latency of a small call (PlanOptions::latency)
     // Referenced pieces of the caller's read pools, packed back to back on the device: bytes
     // [src, src + len) of each of the five pools go to device pool offset dst.
     struct Segment { int64_t src, len, dst; };

@@ -28,8 +28,10 @@ bool choose_class(int rslen, const PlanOptions &opt, KClass *out)
     }
     if (hp) {
         // Haplotype-pair kernels: the tallest register tile that fits wins (fewest lanes: least
-        // wavefront fill, shuffles and sums amortised over the most rows).
-        for (int lanes = 8; lanes <= 32; lanes *= 2)
+        // wavefront fill, shuffles and sums amortised over the most rows).  A small call (one active region)
+        // leaves most of the device idle and waits for its longest task: there the shortest tile wins --
+        // 32 lanes per read, half the rows per step of the 16-lane class and twice the tasks.
+        for (int lanes = opt.latency == 1 ? 32 : 8; lanes <= 32; lanes *= 2)
             if (rows <= lanes * MAX_KH_HP) { *out = KClass{(rows + lanes - 1) / lanes, lanes, 2, 0, 1}; return true; }
         *out = KClass{LONG_KH, 32, 2, 1, 0};
         return true;
@@ -49,7 +51,7 @@ static int scalar_class_of(int rslen)
     return kh <= MAX_KH_SCALAR ? kh : 0;
 }
 
-int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, std::string *err)
+int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *plan, std::string *err)
 {
     char msg[256];
     auto fail = [&](int code, const char *m) { if (err) *err = m; return code; };
@@ -62,6 +64,15 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
     Plan &P = *plan;
     P = Plan();
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) P.resc_cap[k] = 0;
+    PlanOptions opt = opt_in;
+    if (opt.latency < 0) {
+        // tasks if every read took one warp per pair of haplotypes: fewer than a quarter of the resident warps
+        int64_t t = 0;
+        for (int64_t b = 0; b < fb.n_batches && t < opt.resident_warps; ++b)
+            t += (int64_t)std::max(fb.batch_num_reads[b], 0) * ((std::max(fb.batch_num_haps[b], 0) + 1) / 2);
+        opt.latency = t < opt.resident_warps / 4 ? 1 : 0;
+    }
+    P.latency = opt.latency;
 
     // ---- validate tables, count ---------------------------------------------------------------
     int64_t nr = 0, nh = 0;
@@ -254,8 +265,12 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
     // adaptive run length: aim at >= 3 tasks per resident warp, but keep runs long enough that
     // the wavefront fill (<= 31 steps) stays small
     int seg_cols = opt.seg_cols > 0 ? opt.seg_cols : 4096;
-    if (opt.seg_cols <= 0)
+    if (opt.seg_cols <= 0) {
         while (seg_cols > 512 && count_tasks(seg_cols) < 3 * (int64_t)opt.resident_warps) seg_cols /= 2;
+        // one active region per call: most warps of the device have nothing to do and the longest run is the
+        // latency of the call, so the fill no longer matters -- down to one haplotype per run
+        while (opt.latency == 1 && seg_cols > 64 && count_tasks(seg_cols) < (int64_t)opt.resident_warps / 4) seg_cols /= 2;
+    }
 
     struct Run { int64_t b; int k0, k1; int32_t cols; };
     std::vector<Run> runs[2];                  // [0] single runs (classic classes), [1] run pairs: 2j, 2j + 1

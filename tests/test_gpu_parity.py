@@ -120,7 +120,8 @@ def test_host_entry_points_agree():
 
 def test_host_entry_point_pipelines_chunks():
     # phmm_compute_flat cuts the batches into chunks and overlaps plan + upload of one with the kernels
-    # of the other: any chunk size must give the results of the single device-resident workload
+    # of the other: any chunk size must give the results of the single device-resident workload (bit for bit
+    # with the bit-exact kernels)
     fb = synth.generic(77, 23, (5, 40), (1, 9), (20, 300), (30, 500), q_rng=(6, 45), subst=0.05, foreign_frac=0.2)
     ref = oracle.run_port(fb)
     for fast in (False, True):
@@ -130,7 +131,15 @@ def test_host_entry_point_pipelines_chunks():
             out, st = eng.compute(fb, stats=True)
             out2 = eng.compute(fb, out=np.empty(fb.n_pairs))        # arenas reused
             eng.close()
-            assert np.array_equal(out, res[0]) and np.array_equal(out2, out)
+            r = ref.rescued.astype(bool)
+            if fast:
+                # the low bits of the fast FP32 kernels depend on the class a read runs in, and the planner
+                # picks classes by the size of the chunk (small calls: 32 lanes per read); the FP64 classes do not
+                assert np.array_equal(out[r], res[0][r])
+                assert same_or_close(out[~r], ref.out[~r], RTOL_FP32)
+            else:
+                assert np.array_equal(out, res[0])
+            assert np.array_equal(out2, out)
             assert st["n_pairs"] == fb.n_pairs and st["n_cells"] == fb.n_cells
             assert st["n_rescued"] == int(ref.rescued.sum())
     assert same_or_close(res[0][ref.rescued == 0], ref.out[ref.rescued == 0], RTOL_FP32)
@@ -284,12 +293,16 @@ def test_gatk_shaped_api():
         regs = _regions(fb)
         one_by_one = np.concatenate([g.compute_likelihoods(r, h) for r, h in regs])
         together = np.concatenate(g.compute_regions(regs))
-        assert np.array_equal(one_by_one, together)
         if use_double:
+            assert np.array_equal(one_by_one, together)
             assert same_or_close(together, ref.out, RTOL_FP64)
         else:
             r = ref.rescued.astype(bool)
             assert r.any() and (~r).any()
+            # FP64 classes do not depend on the plan; the low bits of the fast FP32 kernels do (a single region
+            # is planned for latency: 32 lanes per read)
+            assert np.array_equal(one_by_one[r], together[r])
+            assert same_or_close(one_by_one[~r], ref.out[~r], RTOL_FP32)
             assert same_or_close(together[~r], ref.out[~r], RTOL_FP32) and same_or_close(together[r], ref.out[r], RTOL_FP64)
         # empty region, and the errors the reference leaves undefined
         assert len(g.compute_likelihoods([], [b"ACGT"])) == 0
