@@ -66,11 +66,14 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) P.resc_cap[k] = 0;
     PlanOptions opt = opt_in;
     if (opt.latency < 0) {
-        // tasks if every read took one warp per pair of haplotypes: fewer than a quarter of the resident warps
+        // tasks if every read took one warp per pair of haplotypes (~50 us each): below eight per resident warp
+        // the call ends before the throughput plan (long runs, tall tiles, few kernels at once) has filled the
+        // device -- measured on 16 active regions per call: 0.55 ms of FP32 kernels against 0.25
+        const int64_t limit = 8 * (int64_t)opt.resident_warps;
         int64_t t = 0;
-        for (int64_t b = 0; b < fb.n_batches && t < opt.resident_warps; ++b)
+        for (int64_t b = 0; b < fb.n_batches && t < limit; ++b)
             t += (int64_t)std::max(fb.batch_num_reads[b], 0) * ((std::max(fb.batch_num_haps[b], 0) + 1) / 2);
-        opt.latency = t < opt.resident_warps / 4 ? 1 : 0;
+        opt.latency = t < limit ? 1 : 0;
     }
     P.latency = opt.latency;
 
@@ -267,9 +270,9 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
     int seg_cols = opt.seg_cols > 0 ? opt.seg_cols : 4096;
     if (opt.seg_cols <= 0) {
         while (seg_cols > 512 && count_tasks(seg_cols) < 3 * (int64_t)opt.resident_warps) seg_cols /= 2;
-        // one active region per call: most warps of the device have nothing to do and the longest run is the
-        // latency of the call, so the fill no longer matters -- down to one haplotype per run
-        while (opt.latency == 1 && seg_cols > 64 && count_tasks(seg_cols) < (int64_t)opt.resident_warps / 4) seg_cols /= 2;
+        // a few active regions per call: the longest run is the latency of the call, so the fill no longer
+        // matters -- down to one haplotype per run
+        while (opt.latency == 1 && seg_cols > 64 && count_tasks(seg_cols) < 3 * (int64_t)opt.resident_warps) seg_cols /= 2;
     }
 
     struct Run { int64_t b; int k0, k1; int32_t cols; };
