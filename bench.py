@@ -140,13 +140,22 @@ def cpu_sample(fb, target_cells):
     return fb.select_batches(np.arange(min(nb, fb.n_batches)))
 
 
+def host_threads():
+    # every core this process may run on; passed explicitly because torchrun exports OMP_NUM_THREADS=1 to its
+    # ranks when there is more than one
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def run_cpu(fb, kind):
     import oracle
     t = time.perf_counter()
     if kind == "reference":
-        oracle.run_ref(fb, nthreads=0)
+        oracle.run_ref(fb, nthreads=host_threads())
     else:
-        oracle.run_port(fb, nthreads=0)
+        oracle.run_port(fb, nthreads=host_threads())
     return time.perf_counter() - t
 
 
@@ -178,7 +187,7 @@ def cpu_baseline(fb, seconds=12.0):
     import oracle
     oracle.build()
     kind = "reference" if oracle.have_ref() else "port"
-    cores = os.cpu_count() or 1
+    cores = host_threads()
     probe = cpu_sample(fb, 2e8)
     dt = run_cpu(probe, kind)
     rate = probe.n_cells / max(dt, 1e-6)
@@ -189,7 +198,7 @@ def cpu_baseline(fb, seconds=12.0):
         # the same code with x86 flush-to-zero on, as GKL's JNI entry sets it (IntelPairHmm.cc:66-70): the
         # benchmark's C entry leaves it off and pays for denormals in the FP32 pass
         t = time.perf_counter()
-        oracle.run_ref(sample, nthreads=0, ftz=1)
+        oracle.run_ref(sample, nthreads=host_threads(), ftz=1)
         ftz_on = sample.n_cells / (time.perf_counter() - t) / 1e9
     return {"value": sample.n_cells / dt / 1e9, "unit": UNIT, "cores": cores, "kind": kind, "value_ftz_on": ftz_on,
             "sample": "first %d batches of the workload: %d pairs, %.3e cells, %.1f s; %s, OpenMP schedule(dynamic,1) over "
@@ -216,7 +225,7 @@ def reference_arm(args, rank):
     t = [run_cpu(sample, kind) for _ in range(args.steps)]
     ms = 1e3 * float(np.mean(t))
     val = sample.n_cells / (ms * 1e-3) / 1e9
-    cores = os.cpu_count() or 1
+    cores = host_threads()
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
