@@ -569,14 +569,13 @@ phmm_forward_kernel(const KernelParams<T> P)
     }
 }
 
-#ifndef PHMM_F64_MINB3
-#define PHMM_F64_MINB3 7
-#endif
 // Minimum resident groups of four warps per SM requested from ptxas (caps registers per thread).
+// FP64 with KH <= 7 fits 12 warps per SM (168 registers) without spills; KH = 8 would spill and stays at 8
+// warps (measured on C4: 43.0 -> 42.25 ms of FP64 kernels with KH <= 7 at 12 warps, 42.8 with KH = 8 too).
 template <typename T, int KH>
 struct MinBlocks {
     static constexpr int K = KH * (sizeof(T) / 4);
-    static constexpr int value = K <= 2 ? 6 : K <= 4 ? 4 : K <= 6 ? 3 : (sizeof(T) == 8 && KH <= PHMM_F64_MINB3) ? 3 : 2;
+    static constexpr int value = K <= 2 ? 6 : K <= 4 ? 4 : K <= 6 ? 3 : (sizeof(T) == 8 && KH <= 7) ? 3 : 2;
 };
 
 typedef void (*KernelF32)(const KernelParams<float>);
