@@ -89,6 +89,7 @@ struct phmm_ctx {
     int force_kh = 0, force_lanes = 0;
     int no_hp = 0;     // PHMM_NO_HP=1: fast FP32 kernels in the two-reads packing (A/B measurements)
     int64_t chunk_cells = 0;   // host-buffer entry points: cells per pipelined chunk (0 = default)
+    int plan_mode = 0;         // PHMM_OPT_PLAN
     std::string error;
     std::mutex mu;     // the legacy symbols may be entered from several OpenMP threads
     // resident blocks per SM of each kernel (asked of the runtime once, not at every launch)
@@ -278,6 +279,7 @@ extern "C" int phmm_set_option(phmm_ctx *ctx, int option, int64_t value)
     case PHMM_OPT_SEG_COLS:    if (value < 0 || value > (1 << 24)) break; ctx->seg_cols = (int)value; return PHMM_OK;
     case PHMM_OPT_FORCE_CLASS: ctx->force_kh = (int)(value >> 8); ctx->force_lanes = (int)(value & 255); return PHMM_OK;
     case PHMM_OPT_CHUNK_CELLS: if (value < 0) break; ctx->chunk_cells = value; return PHMM_OK;
+    case PHMM_OPT_PLAN:        if (value < 0 || value > 2) break; ctx->plan_mode = (int)value; return PHMM_OK;
     default: break;
     }
     ctx->error = "phmm_set_option: unknown option or value out of range";
@@ -294,6 +296,7 @@ extern "C" int64_t phmm_get_option(const phmm_ctx *ctx, int option)
     case PHMM_OPT_SEG_COLS: return ctx->seg_cols;
     case PHMM_OPT_FORCE_CLASS: return ((int64_t)ctx->force_kh << 8) | ctx->force_lanes;
     case PHMM_OPT_CHUNK_CELLS: return ctx->chunk_cells;
+    case PHMM_OPT_PLAN: return ctx->plan_mode;
     default: return -1;
     }
 }
@@ -377,6 +380,7 @@ static PlanOptions plan_options(const phmm_ctx *ctx)
     o.force_kh = ctx->force_kh;
     o.force_lanes = ctx->force_lanes;
     o.resident_warps = ctx->sm_count * 16;
+    o.latency = ctx->plan_mode == 0 ? -1 : ctx->plan_mode - 1;
     o.hp = (ctx->fp32_fast && ctx->precision != 2 && !ctx->no_hp) ? 1 : 0;
     return o;
 }

@@ -18,7 +18,8 @@ from .batches import FlatBatches
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libphmm_cuda.so")
 
-OPT_PRECISION, OPT_FP32_KERNEL, OPT_FP64_KERNEL, OPT_SEG_COLS, OPT_FORCE_CLASS, OPT_CHUNK_CELLS = 1, 2, 3, 4, 6, 7
+OPT_PRECISION, OPT_FP32_KERNEL, OPT_FP64_KERNEL, OPT_SEG_COLS, OPT_FORCE_CLASS, OPT_CHUNK_CELLS, OPT_PLAN = 1, 2, 3, 4, 6, 7, 8
+PLAN_AUTO, PLAN_THROUGHPUT, PLAN_LATENCY = 0, 1, 2
 BOTH, FLOAT_ONLY, DOUBLE_ONLY = 0, 1, 2
 ERRORS = {1: "PHMM_ERR_ARG", 2: "PHMM_ERR_EMPTY_SEQ", 3: "PHMM_ERR_TOO_LONG", 4: "PHMM_ERR_CUDA",
           5: "PHMM_ERR_NOMEM", 6: "PHMM_ERR_PARSE", 7: "PHMM_ERR_IO"}
@@ -349,7 +350,7 @@ class PairHMM:
     """One context on one B200 (phmm_create = the reference's initPairHMM)."""
 
     def __init__(self, device: int = 0, precision: int = BOTH, fast: bool = False, fast64: bool = False,
-                 seg_cols: int = 0, force_class=None, chunk_cells: int = 0):
+                 seg_cols: int = 0, force_class=None, chunk_cells: int = 0, plan: int = PLAN_AUTO):
         self.lib = load_library()
         self._h = C.c_void_p()
         rc = self.lib.phmm_create(C.c_int(device), C.byref(self._h))
@@ -363,6 +364,8 @@ class PairHMM:
             self.set_option(OPT_FORCE_CLASS, (force_class[0] << 8) | force_class[1])
         if chunk_cells:
             self.set_option(OPT_CHUNK_CELLS, chunk_cells)
+        if plan:
+            self.set_option(OPT_PLAN, plan)
 
     def _check(self, rc):
         if rc:

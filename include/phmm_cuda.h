@@ -115,6 +115,12 @@ typedef struct {
 #define PHMM_OPT_CHUNK_CELLS 7   /* host-buffer entry points: cells per pipelined chunk of batches
                                     (0 = default: a fifth of the work, within [4e9, 4e10]); also env PHMM_CHUNK_CELLS */
 
+#define PHMM_OPT_PLAN        8   /* how tasks are cut: 0 by the size of the call (default), 1 for throughput (tall
+                                    register tiles, long runs of haplotypes, four kernels at once), 2 for the latency
+                                    of a small call such as one active region (32 lanes per read, one haplotype per
+                                    run, every class kernel at once); results of the bit-exact kernels do not depend
+                                    on it, the low bits of the fast FP32 kernels do */
+
 typedef struct phmm_ctx phmm_ctx;
 typedef struct phmm_workload phmm_workload;
 

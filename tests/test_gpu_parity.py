@@ -42,10 +42,12 @@ def check(res, ref_out, ref_raw32, ref_raw64, ref_resc, bit_exact32, bit_exact64
 
 
 @pytest.mark.parametrize("name", GOLDEN_NAMES)
-@pytest.mark.parametrize("variant", ["exact", "fast", "fast64"])
+@pytest.mark.parametrize("variant", ["exact", "fast", "fast-throughput-plan", "fast-latency-plan", "fast64"])
 def test_golden_vectors(name, variant):
     fb, g = load_golden(name)
-    kw = {"exact": dict(), "fast": dict(fast=True), "fast64": dict(fast64=True)}[variant]
+    # the golden sets are small, so "fast" alone takes the plan of a small call; the other two force each plan
+    kw = {"exact": dict(), "fast": dict(fast=True), "fast-throughput-plan": dict(fast=True, plan=phmm.PLAN_THROUGHPUT),
+          "fast-latency-plan": dict(fast=True, plan=phmm.PLAN_LATENCY), "fast64": dict(fast64=True)}[variant]
     res, _ = run(fb, **kw)
     check(res, g["out"], g["raw32"], g["raw64"], g["rescued"], variant in ("exact", "fast64"),
           variant != "fast64")
@@ -160,7 +162,9 @@ def test_random_workloads_against_the_oracle():
                              foreign_frac=0.15),
                synth.c1_small(0.04), synth.c4_stress(800), synth.c5_skewed(4000)):
         ref = oracle.run_port(fb)
-        for kw, e32 in ((dict(), True), (dict(fast=True, fast64=True), False)):
+        for kw, e32 in ((dict(), True), (dict(plan=phmm.PLAN_THROUGHPUT), True),
+                        (dict(fast=True, fast64=True, plan=phmm.PLAN_THROUGHPUT), False),
+                        (dict(fast=True, fast64=True, plan=phmm.PLAN_LATENCY), False)):
             res, _ = run(fb, **kw)
             check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, e32, e32)
 
