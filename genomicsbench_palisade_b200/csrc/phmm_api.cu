@@ -74,6 +74,7 @@ struct Arena {
 struct phmm_ctx {
     int device = 0;
     int sm_count = 0;
+    int canary = 0;           // PHMM_CANARY=1: red zones behind every device buffer, checked after each run
     // slot 0 also serves the device-resident workload API; the host-buffer entry points pipeline
     // chunks of batches through all slots (plan + upload of one chunk under the kernels of the others)
     static const int N_SLOTS = 3;
@@ -132,6 +133,9 @@ struct phmm_workload {
     int launches = 0;                 // kernels of the last launch
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};   // timing of the last launch: start, FP32 done, FP64 done
     int64_t last_rescued = 0, last_rescued_cells = 0, last_guard = 0;
+    // PHMM_CANARY: [begin, end) of the red zone behind each buffer (the rounding slack + 256 bytes of 0xA5)
+    struct RedZone { const char *name; uint8_t *begin; size_t len; };
+    std::vector<RedZone> redzones;
 };
 
 namespace {
@@ -227,6 +231,7 @@ extern "C" int phmm_create(int device, phmm_ctx **out)
     ctx->sm_count = prop.multiProcessorCount;
     if (const char *s = getenv("PHMM_FORCE_CLASS")) sscanf(s, "%d,%d", &ctx->force_kh, &ctx->force_lanes);
     if (const char *s = getenv("PHMM_NO_HP")) ctx->no_hp = atoi(s);
+    if (const char *s = getenv("PHMM_CANARY")) ctx->canary = atoi(s);
     if (const char *s = getenv("PHMM_CHUNK_CELLS")) ctx->chunk_cells = atoll(s);
     auto bail = [&](const char *what, cudaError_t err) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
@@ -458,25 +463,26 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
 
     // ---- one allocation, carved into 256-byte aligned pieces ------------------------------------
     const size_t np = (size_t)std::max<int64_t>(1, P.n_pairs);
-    struct Piece { void **ptr; size_t bytes; };
+    struct Piece { void **ptr; size_t bytes; const char *name; };
     const Piece pieces[] = {
-        {(void **)&w->d_pool, (size_t)(5 * w->pool_stride)},
-        {(void **)&w->d_stream, P.stream.size()},
-        {(void **)&w->d_hap_len, P.hap_len.size() * sizeof(int32_t)},
-        {(void **)&w->d_reads, P.reads.size() * sizeof(ReadRec)},
-        {(void **)&w->d_tasks, (size_t)ntasks * sizeof(Task)},
-        {(void **)&w->d_htasks, (size_t)nhtasks * sizeof(HTask)},
-        {(void **)&w->d_ints, INTS_TOTAL * sizeof(int32_t)},
-        {(void **)&w->d_out, np * sizeof(double)},
-        {(void **)&w->d_raw64, np * sizeof(double)},
-        {(void **)&w->d_raw32, np * sizeof(float)},
-        {(void **)&w->d_rescued, np},
-        {(void **)&w->d_resc, need_resc ? (size_t)tot * sizeof(Task) : 0},
-        {(void **)&w->d_guard, need_resc ? (size_t)tot * sizeof(Task) : 0},
-        {(void **)&w->d_scratch, (size_t)(w->scratch_stride * w->scratch_blocks * WARPS_PER_BLOCK) * sizeof(double)},
+        {(void **)&w->d_pool, (size_t)(5 * w->pool_stride), "read pools"},
+        {(void **)&w->d_stream, P.stream.size(), "haplotype stream"},
+        {(void **)&w->d_hap_len, P.hap_len.size() * sizeof(int32_t), "hap_len"},
+        {(void **)&w->d_reads, P.reads.size() * sizeof(ReadRec), "reads"},
+        {(void **)&w->d_tasks, (size_t)ntasks * sizeof(Task), "tasks"},
+        {(void **)&w->d_htasks, (size_t)nhtasks * sizeof(HTask), "htasks"},
+        {(void **)&w->d_ints, INTS_TOTAL * sizeof(int32_t), "ints"},
+        {(void **)&w->d_out, np * sizeof(double), "out"},
+        {(void **)&w->d_raw64, np * sizeof(double), "raw64"},
+        {(void **)&w->d_raw32, np * sizeof(float), "raw32"},
+        {(void **)&w->d_rescued, np, "rescued"},
+        {(void **)&w->d_resc, need_resc ? (size_t)tot * sizeof(Task) : 0, "rescue list"},
+        {(void **)&w->d_guard, need_resc ? (size_t)tot * sizeof(Task) : 0, "guard list"},
+        {(void **)&w->d_scratch, (size_t)(w->scratch_stride * w->scratch_blocks * WARPS_PER_BLOCK) * sizeof(double), "scratch"},
     };
+    const size_t red = ctx->canary ? 256 : 0;
     size_t total = 0;
-    for (const Piece &p : pieces) total += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255;
+    for (const Piece &p : pieces) total += ((std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255) + red;
     uint8_t *base = nullptr;
     if (arena) {
         if (arena->cap < total) {
@@ -503,7 +509,9 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
         size_t off = 0;
         for (const Piece &p : pieces) {
             *p.ptr = base + off;
-            off += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255;
+            const size_t span = ((std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255) + red;
+            if (red) w->redzones.push_back({p.name, base + off + p.bytes, span - p.bytes});
+            off += span;
         }
     }
 
@@ -551,6 +559,10 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     if (stage) WL_TRY(cudaMemcpyAsync(base, stage, upload_extent, cudaMemcpyHostToDevice, up));
     WL_TRY(cudaMemsetAsync(w->d_raw64, 0, np * sizeof(double), up));
     WL_TRY(cudaMemsetAsync(w->d_rescued, 0, np, up));
+    // after the uploads (the staged copy covers the upload pieces' zones), before any kernel of this workload
+    for (const phmm_workload::RedZone &z : w->redzones) WL_TRY(cudaMemsetAsync(z.begin, 0xA5, z.len, up));
+    // PHMM_CANARY=2 (tests): damage one zone on purpose so that the check itself is exercised
+    if (ctx->canary == 2 && !w->redzones.empty()) WL_TRY(cudaMemsetAsync(w->redzones.back().begin + 7, 0, 1, up));
 #undef WL_TRY
     w->h2d_bytes = h2d;
     // host copies of the bulky plan parts are no longer needed
@@ -796,6 +808,20 @@ static int wl_finish(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, phmm_stats 
     }
     w->last_rescued = nres;
     w->last_guard = nguard;
+    if (!w->redzones.empty()) {
+        // every kernel of the run has finished (ss.main joined the side streams and is synchronised)
+        std::vector<uint8_t> host;
+        for (const phmm_workload::RedZone &z : w->redzones) {
+            host.resize(z.len);
+            CUDA_TRY(ctx, cudaMemcpy(host.data(), z.begin, z.len, cudaMemcpyDeviceToHost));
+            for (size_t k = 0; k < z.len; ++k)
+                if (host[k] != 0xA5) {
+                    ctx->error = std::string("PHMM_CANARY: out-of-bounds write ") + std::to_string(k) +
+                                 " bytes behind the end of device buffer '" + z.name + "'";
+                    return PHMM_ERR_CUDA;
+                }
+        }
+    }
     if (stats) {
         memset(stats, 0, sizeof *stats);
         stats->n_pairs = w->n_pairs;

@@ -423,3 +423,33 @@ def test_full_size_properties():
     n = sub.n_pairs
     assert np.array_equal(raw32[:n].view(np.uint32), ref.raw32.view(np.uint32))
     assert np.array_equal(resc[:n], ref.rescued)
+
+
+def test_red_zones_behind_device_buffers_stay_intact(monkeypatch):
+    # compute-sanitizer is closed on the GPU pool, so out-of-bounds writes are looked for with the library's
+    # own red zones (PHMM_CANARY=1: 0xA5 behind every device buffer of a workload, verified after each run)
+    # over every kernel family: register-tile classes, haplotype-pair classes, multi-pass, FP64 rescue,
+    # guard band, both plans, and the chunked host-buffer entry point
+    monkeypatch.setenv("PHMM_CANARY", "1")
+    fbs = [synth.generic(61, 8, (1, 40), (1, 12), (1, 255), (1, 700), q_rng=(6, 45), subst=0.08, foreign_frac=0.2),
+           synth.generic(62, 3, (3, 6), (2, 5), (256, 1500), (50, 2500), q_rng=(6, 45), subst=0.05, foreign_frac=0.3),
+           synth.c4_stress(300)]
+    for fb in fbs:
+        ref = oracle.run_port(fb)
+        for kw, e32 in ((dict(), True), (dict(fast=True, fast64=True, plan=phmm.PLAN_THROUGHPUT), False),
+                        (dict(fast=True, fast64=True, plan=phmm.PLAN_LATENCY), False)):
+            res, _ = run(fb, **kw)
+            check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, e32, e32)
+        eng = phmm.PairHMM(fast=True, chunk_cells=max(1, fb.n_cells // 5))
+        out = eng.compute(fb)
+        eng.close()
+        r = ref.rescued.astype(bool)
+        assert same_or_close(out[~r], ref.out[~r], RTOL_FP32) and same_or_close(out[r], ref.out[r], RTOL_FP64)
+    # the check itself: PHMM_CANARY=2 damages one zone on purpose and the run must report it
+    monkeypatch.setenv("PHMM_CANARY", "2")
+    eng = phmm.PairHMM()
+    w = eng.workload(fbs[0])
+    with pytest.raises(phmm.PhmmError, match="PHMM_CANARY"):
+        w.run()
+    w.close()
+    eng.close()

@@ -4,6 +4,9 @@
 # synccheck (__shfl_*_sync / __syncwarp masks).  SURVEY.md section 5 asks for these three.
 # Run on a GPU box: gpurun --timeout 1200 -- 'bash tools/sanitize.sh'
 # Output: gpurun_out/sanitize_<tool>.log (the last lines hold the ERROR SUMMARY).
+# NOTE: on this round's GPU pool compute-sanitizer is closed by the operators (every pass answers
+# "compute-sanitizer is closed on this pool", exit 86); the script is kept for pools where it is open.
+# Out-of-bounds writes are looked for with the library's own red zones instead (PHMM_CANARY=1).
 set -u
 mkdir -p gpurun_out
 rc=0
