@@ -75,6 +75,10 @@ struct sw_ctx {
 
 struct sw_workload {
     sw_ctx *ctx = nullptr;
+    // SW_CANARY=1: red zone (rounding slack + 256 bytes of 0xA5) behind every device buffer, verified by
+    // sw_workload_results after the kernels; SW_CANARY=2 damages one on purpose (the test of the check)
+    struct RedZone { const char *name; uint8_t *begin; size_t len; };
+    std::vector<RedZone> redzones;
     int64_t n_pairs = 0, n_cells = 0, h2d_bytes = 0, bt_bytes = 0;
     int32_t cigar_stride = 0;
     int32_t class_ntasks[N_CLASSES] = {0};
@@ -283,18 +287,22 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
     auto fail = [&](int code) { sw_workload_destroy(w); return code; };
     if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->error = "cudaSetDevice failed"; return fail(SW_ERR_CUDA); }
     const size_t np = (size_t)std::max<int64_t>(1, n);
-    struct Piece { void **ptr; size_t bytes; };
+    struct Piece { void **ptr; size_t bytes; const char *name; };
     const Piece pieces[] = {
-        {(void **)&w->d_ref, (size_t)(rhi - rlo)}, {(void **)&w->d_alt, (size_t)(ahi - alo)},
-        {(void **)&w->d_pairs, np * sizeof(PairRec)},
-        {(void **)&w->d_score, np * 4}, {(void **)&w->d_offset, np * 4}, {(void **)&w->d_cigar_len, np * 4},
-        {(void **)&w->d_counters, 64 * 4},
-        {(void **)&w->d_cigar, np * (size_t)cigar_stride},
-        {(void **)&w->d_bt, (size_t)bt_words * 4},
-        {(void **)&w->d_elems, (size_t)(warps_sum * w->elems_stride) * sizeof(int2)},
+        {(void **)&w->d_ref, (size_t)(rhi - rlo), "ref pool"}, {(void **)&w->d_alt, (size_t)(ahi - alo), "alt pool"},
+        {(void **)&w->d_pairs, np * sizeof(PairRec), "pairs"},
+        {(void **)&w->d_score, np * 4, "score"}, {(void **)&w->d_offset, np * 4, "offset"},
+        {(void **)&w->d_cigar_len, np * 4, "cigar_len"},
+        {(void **)&w->d_counters, 64 * 4, "counters"},
+        {(void **)&w->d_cigar, np * (size_t)cigar_stride, "cigar"},
+        {(void **)&w->d_bt, (size_t)bt_words * 4, "backtrack words"},
+        {(void **)&w->d_elems, (size_t)(warps_sum * w->elems_stride) * sizeof(int2), "cigar elements"},
     };
+    const char *canary_env = getenv("SW_CANARY");
+    const int canary = canary_env ? atoi(canary_env) : 0;
+    const size_t red = canary ? 256 : 0;
     size_t total = 0;
-    for (const Piece &p : pieces) total += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255;
+    for (const Piece &p : pieces) total += ((std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255) + red;
     cudaError_t e = cudaSuccess;
     if (arena_slot) {
         // steady-state calls never pay cudaMalloc / cudaFree (both synchronise the device)
@@ -314,8 +322,15 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
         return fail(e == cudaErrorMemoryAllocation ? SW_ERR_NOMEM : SW_ERR_CUDA);
     }
     size_t off = 0;
-    for (const Piece &p : pieces) { *p.ptr = w->d_base + off; off += (std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255; }
+    for (const Piece &p : pieces) {
+        *p.ptr = w->d_base + off;
+        const size_t span = ((std::max<size_t>(p.bytes, 1) + 255) & ~(size_t)255) + red;
+        if (red) w->redzones.push_back({p.name, w->d_base + off + p.bytes, span - p.bytes});
+        off += span;
+    }
     cudaStream_t st = w->slot->stream;
+    for (const sw_workload::RedZone &z : w->redzones) cudaMemsetAsync(z.begin, 0xA5, z.len, st);
+    if (canary == 2 && !w->redzones.empty()) cudaMemsetAsync(w->redzones.back().begin + 7, 0, 1, st);
     if (n) {
         if ((e = cudaMemcpyAsync(w->d_ref, fp->ref_pool + rlo, (size_t)(rhi - rlo), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
             (e = cudaMemcpyAsync(w->d_alt, fp->alt_pool + alo, (size_t)(ahi - alo), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
@@ -410,6 +425,17 @@ extern "C" int sw_workload_results(sw_ctx *ctx, sw_workload *w, int32_t *score, 
     if (cigar_len) SW_TRY(ctx, cudaMemcpyAsync(cigar_len, w->d_cigar_len, n * 4, cudaMemcpyDeviceToHost, st));
     if (cigar) SW_TRY(ctx, cudaMemcpyAsync(cigar, w->d_cigar, n * (size_t)w->cigar_stride, cudaMemcpyDeviceToHost, st));
     SW_TRY(ctx, cudaStreamSynchronize(st));
+    std::vector<uint8_t> host;
+    for (const sw_workload::RedZone &z : w->redzones) {
+        host.resize(z.len);
+        SW_TRY(ctx, cudaMemcpy(host.data(), z.begin, z.len, cudaMemcpyDeviceToHost));
+        for (size_t k = 0; k < z.len; ++k)
+            if (host[k] != 0xA5) {
+                ctx->error = std::string("SW_CANARY: out-of-bounds write ") + std::to_string(k) +
+                             " bytes behind the end of device buffer '" + z.name + "'";
+                return SW_ERR_CUDA;
+            }
+    }
     return SW_OK;
 }
 

@@ -193,3 +193,28 @@ def test_gpu_full_size_properties():
     ref = osw.run_port(ps.select(idx), pm, sw.SOFTCLIP)
     assert ref.cigars == [cig[k] for k in idx] and np.array_equal(ref.score, res.score[idx])
     eng.close()
+
+
+@pytest.mark.gpu
+def test_gpu_red_zones_behind_device_buffers_stay_intact(monkeypatch):
+    # compute-sanitizer is closed on the GPU pool: SW_CANARY=1 puts 0xA5 red zones behind every device buffer
+    # (pools, results, backtrack words, CIGAR elements) and sw_workload_results verifies them after the kernels
+    monkeypatch.setenv("SW_CANARY", "1")
+    eng = sw.SmithWaterman()
+    sets = [sw_pairs.synth(15, 300, ref_rng=(1, 300), snp=0.03, indel=0.01, read_like=0.4),
+            sw_pairs.synth(16, 40, ref_rng=(600, 1024), alts_per_ref=(2, 6), snp=0.02, indel=0.01),
+            sw_pairs.synth(17, 100, ref_rng=(30, 400), snp=0.25, indel=0.08),
+            sw_pairs.full_length_cases(),
+            sw_pairs.from_lists([(b"A" * 1024, b"C" * 1024), (b"A" * 1023, b"C" * 1024)])]
+    for ps in sets:
+        for pm in ((200, -150, -260, -11), (100, -100000, -100000, -100000)):
+            for st in STRATEGIES:
+                ref = osw.run_port(ps, pm, st)
+                got = eng.align_pairs(ps, pm, st, stride=16)        # a short stride: overflow + retry path too
+                assert got.cigars == ref.cigars
+                assert np.array_equal(got.offset, ref.offset) and np.array_equal(got.score, ref.score)
+    # the check itself: SW_CANARY=2 damages one zone on purpose and the call must report it
+    monkeypatch.setenv("SW_CANARY", "2")
+    with pytest.raises(sw.SwError, match="SW_CANARY"):
+        eng.align_pairs(sets[0], (200, -150, -260, -11), STRATEGIES[0])
+    eng.close()
