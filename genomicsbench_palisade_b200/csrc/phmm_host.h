@@ -66,6 +66,23 @@ bool choose_class(int rslen, const PlanOptions &opt, KClass *kc);
 // Builds the plan; on failure returns a PHMM_ERR_* code and fills `err`.
 int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, std::string *err);
 
+// ---- cost model of the scheduler (phmm_cost.cpp) -------------------------------------------------
+// Device time of a read against one haplotype column = lanes x (rows per thread + step_rows) row steps of its
+// kernel class; an FP64 row step costs f64_row_cost FP32 ones, a row step of the bit-exact FP32 kernels (two reads
+// per thread, unfused) exact_row_cost.  Calibrated on B200 (tools/class_sweep.py); PHMM_COST_MODEL overrides.
+struct CostModel {
+    double step_rows_fast = 2.5;      // per-step overhead of a lane in rows: shuffles, LDS, loop control
+    double step_rows_exact = 1.5;
+    double step_rows_f64 = 1.5;
+    double f64_row_cost = 2.3;
+    double exact_row_cost = 0.9;
+};
+CostModel default_cost_model();
+// cost[b]: predicted time of batch b (arbitrary unit); read_rescued (may be NULL): 1 where the predictor expects
+// most pairs of the read to be re-run in FP64.
+int batch_costs(const phmm_flat_batches &fb, int fast, int precision, const CostModel &m, int64_t *cost,
+                uint8_t *read_rescued);
+
 // ---- kernels (phmm_inst_*.cu, phmm_microbench.cu) -------------------------------------------
 typedef void (*KernelF32)(const KernelParams<float>);
 typedef void (*KernelF64)(const KernelParams<double>);

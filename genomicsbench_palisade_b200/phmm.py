@@ -57,7 +57,7 @@ class CTestcase(C.Structure):
 EXPORTS = ["phmm_abi_version", "phmm_device_count", "phmm_create", "phmm_destroy", "phmm_set_option",
            "phmm_get_option", "phmm_last_error", "phmm_compute_pairs", "phmm_compute_batches",
            "phmm_compute_flat", "phmm_workload_create", "phmm_workload_run", "phmm_workload_results",
-           "phmm_workload_destroy", "phmm_partition_lpt", "phmm_parse_file", "phmm_parse_buffer",
+           "phmm_workload_destroy", "phmm_partition_lpt", "phmm_batch_costs", "phmm_parse_file", "phmm_parse_buffer",
            "phmm_parsed_batches", "phmm_parsed_free", "phmm_microbench", "phmm_get_tables",
            "phmm_plan_summary", "phmm_cache_write", "phmm_cache_open", "phmm_gatk_init",
            "phmm_gatk_compute_likelihoods", "phmm_gatk_compute_regions", "phmm_gatk_done",
@@ -274,6 +274,19 @@ def partition_lpt(cost, parts: int) -> np.ndarray:
     if rc:
         raise PhmmError(rc, "phmm_partition_lpt")
     return owner
+
+
+def batch_costs(fb: FlatBatches, fast: bool = True, precision: int = BOTH, predicted=False):
+    """Predicted device time per batch (phmm_batch_costs): the cost to hand to partition_lpt."""
+    lib = load_library()
+    keep = _Keep(fb)
+    cost = np.zeros(max(1, fb.n_batches), np.int64)
+    pred = np.zeros(max(1, len(fb.read_len)), np.uint8)
+    rc = lib.phmm_batch_costs(C.byref(keep.c), C.c_int(int(fast)), C.c_int(precision), _ptr(cost), _ptr(pred))
+    if rc:
+        raise PhmmError(rc, "phmm_batch_costs")
+    cost = cost[:fb.n_batches]
+    return (cost, pred[:len(fb.read_len)]) if predicted else cost
 
 
 def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True, fast=False):

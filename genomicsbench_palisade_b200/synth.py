@@ -96,7 +96,38 @@ def _assemble(rng, bnr, bnh, hap_len, hap_pool, read_len, meta, **kw):
     hap_len = np.asarray(hap_len, np.int64)
     hap_off = np.concatenate(([0], np.cumsum(hap_len)))[:-1]
     rl, roff, rs, q, i, d, c = _gen_reads(rng, bnr, bnh, hap_len, hap_off, hap_pool, read_len, **kw)
+    meta = dict(meta, gen=dict(kw))
     return FlatBatches(bnr, bnh, rl, roff, rs, q, i, d, c, hap_len, hap_off, hap_pool, meta)
+
+
+def same_shape(fb, content_seed, jitter=8, n_snps=3):
+    """A set with exactly the shape of `fb` (batch sizes, every read and haplotype length, hence the
+    same cell count) and new content: per batch a fresh base sequence, every haplotype a window of it
+    plus a few substitutions, reads drawn from the new haplotypes with the quality / substitution
+    parameters `fb` was generated with.  The parts of a weak-scaling run are made this way, so that
+    every GPU gets the work the single GPU gets at N = 1."""
+    rng = np.random.Generator(np.random.PCG64(content_seed))
+    bnh = fb.batch_num_haps.astype(np.int64)
+    hap_len = fb.hap_len.astype(np.int64)
+    nh = len(hap_len)
+    bid = np.repeat(np.arange(len(bnh)), bnh)
+    ext = np.zeros(len(bnh), np.int64)
+    np.maximum.at(ext, bid, hap_len)
+    ext += 2 * jitter
+    base_off = np.concatenate(([0], np.cumsum(ext)))[:-1]
+    base_pool = _rand_bases(rng, int(ext.sum()))
+    start = np.minimum(rng.integers(0, 2 * jitter + 1, nh), ext[bid] - hap_len)
+    hoff = np.concatenate(([0], np.cumsum(hap_len)))[:-1]
+    hid = np.repeat(np.arange(nh), hap_len)
+    pos = np.arange(int(hap_len.sum())) - hoff[hid]
+    pool = base_pool[base_off[bid][hid] + start[hid] + pos].copy()
+    for _ in range(n_snps):
+        on = rng.random(nh) < 0.6
+        p = hoff + (rng.random(nh) * hap_len).astype(np.int64)
+        pool[p[on]] = ACGT[rng.integers(0, 4, int(on.sum()))]
+    meta = dict(fb.meta, content_seed=content_seed)
+    gen = meta.pop("gen")
+    return _assemble(rng, fb.batch_num_reads, fb.batch_num_haps, hap_len, pool, fb.read_len.astype(np.int64), meta, **gen)
 
 
 def generic(seed, n_batches, reads_rng, haps_rng, rlen_rng, hlen_rng, q_rng=(10, 40), subst=0.01,

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define PHMM_ABI_VERSION 3
+#define PHMM_ABI_VERSION 4
 
 /* ---- status codes (the reference defines none: it asserts / exit(0)s) ---- */
 #define PHMM_OK              0
@@ -178,6 +178,16 @@ int phmm_workload_destroy(phmm_workload *w);
  * Longest-processing-time-first assignment of n items (batches) with the given costs (cells) to
  * `parts` devices; owner[k] in [0, parts).  Deterministic, so every rank computes the same map. */
 int phmm_partition_lpt(const int64_t *cost, int64_t n, int parts, int32_t *owner);
+/* Predicted device time of every batch (arbitrary unit), the cost phmm_partition_lpt should be given.  The
+ * reference has no counterpart: its only per-batch figure is Batch::num_cells
+ * (benchmarks/phmm/PairHMMUnitTest_orig.cpp:166), which ignores that the device pays for the register tile of
+ * a read's kernel class (padded rows + a per-step overhead per lane) and that a pair below MIN_ACCEPTED is
+ * computed twice, the second time in FP64 (IntelPairHmmCSource.cpp:73-75).  fp32_fast / precision as
+ * PHMM_OPT_FP32_KERNEL / PHMM_OPT_PRECISION.  The FP64 share is predicted per read on the host, without dynamic
+ * programming, from a k-mer anchored quality-weighted mismatch score against the first haplotype of the batch;
+ * read_rescued (may be NULL, [n_reads]) receives 1 where most pairs of the read are expected to be rescued. */
+int phmm_batch_costs(const phmm_flat_batches *fb, int fp32_fast, int precision, int64_t *cost,
+                     uint8_t *read_rescued);
 
 /* ---- text input (the reference's on-disk format) ---------------------------------------------
  * Parses what read_testfile / read_batch read (PairHMMUnitTest_orig.cpp:97-213) into flat

@@ -49,4 +49,4 @@ def max_rel(a, b):
     return float(np.nanmax(rel)) if rel.size else 0.0
 
 
-GOLDEN_NAMES = ["kat", "tiny", "edge", "c1_small", "c2_large", "c4_stress"]
+GOLDEN_NAMES = ["kat", "tiny", "edge", "c1_small", "c2_large", "c3_regions", "c4_stress"]

@@ -49,6 +49,13 @@ def main():
                                    foreign_frac=0.08, name="golden-c1"))
     save("c2_large", synth.generic(synth.SEED0 + 22, 2, (40, 60), (16, 24), (100, 250), (150, 473),
                                    foreign_frac=0.04, name="golden-c2"))
+    # C3 shape (active regions, 250 bp reads x all candidate haplotypes) with 25 % unrelated reads so that the
+    # FP64-rescue path of this shape is pinned too
+    c3 = synth.c3_regions(3, seed=synth.SEED0 + 23)
+    gen = dict(c3.meta["gen"], foreign_frac=0.25)
+    rng = np.random.Generator(np.random.PCG64(synth.SEED0 + 123))
+    save("c3_regions", synth._assemble(rng, c3.batch_num_reads, c3.batch_num_haps, c3.hap_len, c3.hap,
+                                       c3.read_len.astype(np.int64), {"workload": "golden-c3"}, **gen))
     save("c4_stress", synth.generic(synth.SEED0 + 24, 3, (6, 6), (4, 4), (200, 250), (1000, 5000),
                                     q_rng=(6, 15), subst=0.20, name="golden-c4"))
 

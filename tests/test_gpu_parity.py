@@ -169,6 +169,56 @@ def test_random_workloads_against_the_oracle():
             check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, e32, e32)
 
 
+def cpu_reference(fb):
+    """The reference's own AVX code when oracle/_ref holds it (it does on the GPU box), else the C restatement."""
+    return oracle.run_ref(fb) if oracle.have_ref() else oracle.run_port(fb)
+
+
+def test_c3_active_regions_against_the_oracle():
+    # BASELINE.json configs[2]: every read 250 bp, all pairs of a region (IntelPairHmm.cc:99-145) -- every read
+    # in one kernel class with both haplotype runs full, a shape no other set produces.  Both plans, the exact
+    # and the fast kernels, and the GATK-shaped entry the upstream caller of this shape uses.
+    fb = synth.c3_regions(24, seed=synth.SEED0 + 33)
+    ref = cpu_reference(fb)
+    assert fb.n_pairs > 30_000 and set(fb.read_len.tolist()) == {250}
+    for kw, e32 in ((dict(plan=phmm.PLAN_THROUGHPUT), True), (dict(plan=phmm.PLAN_LATENCY), True),
+                    (dict(fast=True, fast64=True, plan=phmm.PLAN_THROUGHPUT), False),
+                    (dict(fast=True, fast64=True, plan=phmm.PLAN_LATENCY), False)):
+        res, st = run(fb, **kw)
+        check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, e32, e32)
+    # with a quarter of the reads unrelated to the region, so that the rescue path of this shape runs too
+    fb2, _ = load_golden("c3_regions")
+    ref2 = cpu_reference(fb2)
+    assert 0.05 < ref2.rescued.mean() < 0.95
+    for kw, e32 in ((dict(), True), (dict(fast=True, fast64=True, plan=phmm.PLAN_THROUGHPUT), False)):
+        res, st = run(fb2, **kw)
+        check(res, ref2.out, ref2.raw32, ref2.raw64, ref2.rescued, e32, e32)
+    g = phmm.GatkPairHMM()
+    together = np.concatenate(g.compute_regions(_regions(fb2)))
+    g.done()
+    r = ref2.rescued.astype(bool)
+    assert same_or_close(together[~r], ref2.out[~r], RTOL_FP32) and same_or_close(together[r], ref2.out[r], RTOL_FP64)
+
+
+@pytest.mark.parametrize("name", ["c2", "c5"])
+def test_benchmarked_path_on_a_large_slice(name):
+    # what bench.py times -- fast FP32 + fast FP64 kernels, throughput plan, device-resident and through the
+    # chunked host-buffer call -- on >= 1e5 pairs of the benchmark's own generators against the reference
+    fb = synth.c2_large(200_000) if name == "c2" else synth.c5_skewed(100_000)
+    assert fb.n_pairs >= 100_000
+    ref = cpu_reference(fb)
+    eng = phmm.PairHMM(fast=True, fast64=True)
+    w = eng.workload(fb)
+    st = w.run()
+    res = w.results(raw=True)
+    w.close()
+    check(res, ref.out, ref.raw32, ref.raw64, ref.rescued, False, False)
+    assert st["n_rescued"] == int(ref.rescued.sum()) > 0
+    out = eng.compute(fb)
+    eng.close()
+    assert np.array_equal(out, res[0])
+
+
 def test_every_kernel_class_is_bit_exact():
     # pin each register-tile height / lane-group width in turn on reads that fit it; odd read counts
     # leave f32x2 halves and lane groups idle
@@ -355,8 +405,9 @@ def test_unmodified_reference_driver_linked_against_libphmm_cuda(tmp_path):
     from conftest import ROOT
     cuda = os.path.join(ROOT, "oracle", "_ref", "gkl_example_driver_cuda")
     ref = os.path.join(ROOT, "oracle", "_ref", "gkl_example_driver_ref")
-    if not (os.path.exists(cuda) and os.path.exists(ref)):
-        pytest.skip("driver binaries are built only where /root/reference exists")
+    # built by oracle/build_ref.sh in the build container (where /root/reference exists) and shipped with the
+    # tree; on a box with a GPU their absence is a failure of the build, not a reason to skip the boundary test
+    assert os.path.exists(cuda) and os.path.exists(ref), "oracle/_ref/gkl_example_driver_{cuda,ref} missing: run __graft_entry__.build() where /root/reference exists"
     fb = synth.generic(17, 5, (2, 10), (1, 6), (20, 200), (30, 400), q_rng=(6, 45), foreign_frac=0.3)
     path = str(tmp_path / "in.txt")
     open(path, "wb").write(fb.to_text())

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     # the reference's own C++-linkage symbols (IntelPairHmmCSource.cpp:29,61,89,103; pairhmm_common.cc:3)
     for name in phmm.LEGACY_EXPORTS:
         assert hasattr(lib, name), name
-    assert lib.phmm_abi_version() == 3
+    assert lib.phmm_abi_version() == 4
 
 
 def test_no_cpu_fallback_without_a_device():
@@ -190,6 +190,76 @@ def test_lpt_partition():
         assert np.array_equal(owner, phmm.partition_lpt(cost, parts))   # deterministic across ranks
 
 
+def test_batch_costs_and_rescue_prediction():
+    # phmm_batch_costs: the cost the scheduler balances -- register-tile geometry + predicted FP64 work
+    for fb, lo in ((synth.c2_large(60_000), 0.97), (synth.c1_small(0.05), 0.97), (synth.c5_skewed(20_000), 0.97),
+                   (synth.c4_stress(2_000), 0.80)):
+        cost, pred = phmm.batch_costs(fb, fast=True, predicted=True)
+        assert cost.shape == (fb.n_batches,) and (cost > 0).all()
+        ref = oracle.run_port(fb)
+        bos, brs = fb.batch_out_start, fb.batch_read_start
+        act = np.concatenate([ref.rescued[bos[b]:bos[b + 1]].reshape(int(fb.batch_num_reads[b]), -1).mean(1) >= 0.5
+                              for b in range(fb.n_batches)])
+        assert (pred.astype(bool) == act).mean() >= lo, (pred.mean(), act.mean())
+        # never cheaper than the cells themselves, and FP64-only / FP32-only never dearer than both ... than sensible
+        c32 = phmm.batch_costs(fb, fast=True, precision=phmm.FLOAT_ONLY)
+        assert (c32 <= cost).all() and (c32 >= fb.batch_cells).all()
+    # the all-pairs cost of a batch with many rescued reads exceeds that of its clean twin
+    clean = synth.generic(5, 4, (20, 20), (6, 6), (100, 150), (150, 300), foreign_frac=0.0)
+    dirty = synth.generic(5, 4, (20, 20), (6, 6), (100, 150), (150, 300), foreign_frac=0.9)
+    assert phmm.batch_costs(dirty).sum() > 1.5 * phmm.batch_costs(clean).sum()
+    # LPT over predicted time balances predicted time
+    fb = synth.c2_large(400_000)
+    cost = phmm.batch_costs(fb)
+    owner = phmm.partition_lpt(cost, 2)
+    load = np.bincount(owner, weights=cost, minlength=2)
+    assert load.max() / load.mean() < 1.05
+    empty = synth.generic(1, 0, (1, 2), (1, 2), (10, 20), (10, 20))
+    assert len(phmm.batch_costs(empty)) == 0
+
+
+def test_same_shape_parts_of_a_weak_scaling_run():
+    a = synth.c2_large(60_000)
+    b = synth.same_shape(a, 7)
+    c = synth.same_shape(a, 8)
+    for x in (b, c):
+        assert x.n_cells == a.n_cells and x.n_pairs == a.n_pairs
+        assert np.array_equal(x.read_len, a.read_len) and np.array_equal(x.hap_len, a.hap_len)
+        assert np.array_equal(x.batch_num_reads, a.batch_num_reads)
+    assert (b.rs != c.rs).mean() > 0.5 and (b.hap != a.hap).mean() > 0.5
+    ra, rb = oracle.run_port(a), oracle.run_port(b)
+    assert abs(ra.rescued.mean() - rb.rescued.mean()) < 0.05 and rb.rescued.any()
+    assert np.array_equal(synth.same_shape(a, 7).rs, b.rs)       # deterministic
+
+
+def test_bench_parity_block_and_config():
+    import bench
+    fb, g = load_golden("c2_large")
+    ref = oracle.run_port(fb)
+    ok = bench.parity_block(ref, (ref.out.copy(), ref.rescued.copy()), "fast")
+    assert ok["ok"] and ok["rescue_symdiff"] == 0 and ok["pairs"] == fb.n_pairs and ok["max_rel_fp32"] == 0.0
+    out = ref.out.copy()
+    k = int(np.nonzero(ref.rescued == 0)[0][0])
+    out[k] *= 1 + 5e-4
+    assert not bench.parity_block(ref, (out, ref.rescued.copy()), "fast")["ok"]
+    resc = ref.rescued.copy()
+    resc[k] = 1
+    bad = bench.parity_block(ref, (ref.out.copy(), resc), "fast")
+    assert not bad["ok"] and bad["rescue_symdiff"] == 1
+    out = ref.out.copy()
+    k = int(np.nonzero(ref.rescued == 1)[0][0])
+    out[k] *= 1 + 1e-8
+    assert not bench.parity_block(ref, (out, ref.rescued.copy()), "fast")["ok"]
+    # a prefix: the reference ran on the first pairs only
+    half = fb.select_batches(np.arange(1))
+    rh = oracle.run_port(half)
+    assert bench.parity_block(rh, (ref.out, ref.rescued), "exact")["pairs"] == half.n_pairs
+    # both arms print the same config block
+    tiny = bench.make_workload("tiny", 1)
+    assert bench.config_block("tiny", tiny, 1) == bench.config_block("tiny", bench.make_workload("tiny", 1), 1)
+    assert bench.config_block("tiny", bench.make_workload("tiny", 2), 2)["cells"] == 2 * tiny.n_cells
+
+
 def test_batches_helpers():
     fb, g = load_golden("c1_small")
     rsl, hpl, _, _ = fb.pairs()
@@ -215,13 +285,15 @@ def test_two_rank_sharding_gloo(tmp_path):
         "import bench\n"
         "dist.init_process_group('gloo')\n"
         "rank, world = dist.get_rank(), dist.get_world_size()\n"
-        "fb, mine = bench.make_shard('tiny', rank, world)\n"
+        "fb = bench.make_workload('tiny', world)\n"
+        "mine, idx = bench.shard_of(fb, rank, world, True)\n"
         "t = torch.tensor([mine.n_cells, mine.n_pairs, mine.n_batches], dtype=torch.int64)\n"
         "dist.all_reduce(t)\n"
         "own = torch.zeros(fb.n_batches, dtype=torch.int64)\n"
-        "own[bench.my_batches(fb, rank, world)] = 1\n"
+        "own[idx] = 1\n"
         "dist.all_reduce(own)\n"
         "ok = bool((own == 1).all()) and int(t[0]) == fb.n_cells and int(t[1]) == fb.n_pairs\n"
+        "ok = ok and fb.n_batches == 24 and fb.n_cells == 2 * bench.make_workload('tiny', 1).n_cells\n"
         "if rank == 0: print(json.dumps({'ok': ok, 'cells': int(t[0]), 'world': world}))\n"
         "dist.destroy_process_group()\n" % ROOT)
     env = dict(os.environ, MASTER_ADDR="127.0.0.1")
