@@ -407,7 +407,7 @@ extern "C" int phmm_workload_destroy(phmm_workload *w)
 // behind an event on `up`, or synchronises.
 // `prebuilt`: a plan of `fb` made ahead of time (the planner thread of phmm_compute_flat); it is moved from.
 static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, cudaStream_t up, phmm_workload **out,
-                     Plan *prebuilt = nullptr)
+                     Plan *prebuilt = nullptr, const PlanOptions *popt = nullptr)
 {
     *out = nullptr;
     phmm_workload *w = new phmm_workload();
@@ -417,7 +417,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     std::string err;
     int rc = PHMM_OK;
     if (prebuilt) w->plan = std::move(*prebuilt);
-    else rc = build_plan(*fb, plan_options(ctx), &w->plan, &err);
+    else rc = build_plan(*fb, popt ? *popt : plan_options(ctx), &w->plan, &err);
     if (rc != PHMM_OK) { ctx->error = err; delete w; return rc; }
     Plan &P = w->plan;
     w->n_pairs = P.n_pairs;
@@ -623,13 +623,6 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     pf.guard = w->d_guard; pf.guard_count = w->d_ints + INTS_GUARD;
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) pf.resc_off[k] = w->resc_off[k];
     pf.mode = mode;
-    {
-        // guard band of the fast kernel: |contracted - unfused| <= ~(5 (R + H)) ulp relative on an
-        // all-positive recurrence; 8x that, and never less than 2^-7
-        const double rel = std::max(1.0 / 128, 40.0 * (P.max_rslen + P.max_haplen) * 5.96e-8);
-        pf.guard_lo = (float)(1e-28 * (1.0 - rel));
-        pf.guard_hi = (float)(1e-28 * (1.0 + rel));
-    }
     KernelParams<double> pd;
     memset(&pd, 0, sizeof pd);
     pd.rs = pf.rs; pd.q = pf.q; pd.i = pf.i; pd.d = pf.d; pd.c = pf.c;
@@ -646,8 +639,9 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
 
     // dynamic shared memory (emission table + stream ring + run table per warp) and a grid that
     // fills the device once: the kernels are persistent, warps pull tasks from the queue
-    auto prepare = [&](const void *kernel, int kh, int64_t ntasks, bool longr, int *grid, int *smem, bool hp = false) -> bool {
-        *smem = WARPS_PER_BLOCK * (hp ? smem_per_warp_hp(kh) : smem_per_warp(kh));     // a function of the kernel
+    // layout: 0 = phmm_forward_kernel, 1 = haplotype-pair FP32
+    auto prepare = [&](const void *kernel, int kh, int64_t ntasks, bool longr, int *grid, int *smem, int layout = 0) -> bool {
+        *smem = WARPS_PER_BLOCK * (layout == 1 ? smem_per_warp_hp(kh) : smem_per_warp(kh));     // a function of the kernel
         int nb = 0;
         auto it = ctx->blocks_per_sm.find(kernel);
         if (it != ctx->blocks_per_sm.end()) {
@@ -720,7 +714,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
             pf.htasks = cd.kc.hp ? w->d_htasks + cd.task_off : nullptr;
             pf.ntasks_ptr = w->d_ints + INTS_NTASKS + c;
             pf.counter = w->d_ints + INTS_COUNTER + counter_slot++;
-            if (!prepare((const void *)k, cd.kc.kh, cd.ntasks, cd.kc.longr, &grid, &smem, cd.kc.hp != 0)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
+            if (!prepare((const void *)k, cd.kc.kh, cd.ntasks, cd.kc.longr, &grid, &smem, cd.kc.hp ? 1 : 0)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
             k<<<grid, WARPS_PER_BLOCK * 32, smem, ks>>>(pf);
         }
         CUDA_TRY(ctx, cudaGetLastError());
@@ -929,7 +923,8 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
     std::mutex pmu;
     std::condition_variable pcv;
     bool pstop = false;
-    const PlanOptions popt = plan_options(ctx);
+    PlanOptions popt = plan_options(ctx);
+    popt.latency = plan_latency(*fb, popt);        // one decision for the whole call, not one per chunk
     std::thread planner;
     if (chunks.size() > 1)
         planner = std::thread([&]() {
@@ -962,7 +957,7 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         phmm_flat_batches sub = sub_batches(fb, c);
         StreamSet &ss = ctx->ss[slot];
         const double tc0 = wall_ms();
-        rc = wl_create(ctx, &sub, &ctx->arena[slot], ctx->copy_in, &wl[slot], prebuilt);
+        rc = wl_create(ctx, &sub, &ctx->arena[slot], ctx->copy_in, &wl[slot], prebuilt, &popt);
         if (rc != PHMM_OK) break;
         const double tc1 = wall_ms();
         if (cudaEventRecord(ss.ev_uploaded, ctx->copy_in) != cudaSuccess) { ctx->error = "cudaEventRecord failed"; rc = PHMM_ERR_CUDA; break; }

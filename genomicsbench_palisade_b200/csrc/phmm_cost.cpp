@@ -158,7 +158,7 @@ int batch_costs(const phmm_flat_batches &fb, int fast, int precision, const Cost
         } else if (precision == 2) {
             w = kc.lanes * (kc.kh + m.step_rows_f64) * m.f64_row_cost;
         } else if (kc.hp) {
-            w = kc.lanes * (kc.kh + m.step_rows_fast);
+            w = kc.lanes * (kc.kh + m.step_rows_fast) * (kc.lanes == 8 ? m.lanes8_cost : kc.lanes == 32 ? m.lanes32_cost : 1.0);
         } else {
             w = kc.lanes * (kc.kh + m.step_rows_exact) * m.exact_row_cost * (fast ? 0.8 : 1.0);
         }

@@ -63,6 +63,7 @@ struct Plan {
 
 // Chooses the kernel class for a read length; returns false when no single-pass class fits.
 bool choose_class(int rslen, const PlanOptions &opt, KClass *kc);
+int plan_latency(const phmm_flat_batches &fb, const PlanOptions &opt);
 // Builds the plan; on failure returns a PHMM_ERR_* code and fills `err`.
 int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, std::string *err);
 
@@ -71,11 +72,13 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, 
 // kernel class; an FP64 row step costs f64_row_cost FP32 ones, a row step of the bit-exact FP32 kernels (two reads
 // per thread, unfused) exact_row_cost.  Calibrated on B200 (tools/class_sweep.py); PHMM_COST_MODEL overrides.
 struct CostModel {
-    double step_rows_fast = 2.5;      // per-step overhead of a lane in rows: shuffles, LDS, loop control
-    double step_rows_exact = 1.5;
-    double step_rows_f64 = 1.5;
-    double f64_row_cost = 2.3;
+    double step_rows_fast = 1.6;      // per-step overhead of a lane in rows: shuffles, LDS, loop control
+    double step_rows_exact = 1.5;     //   (fit to profiles/r1_v4_class_sweep.log: 16 lanes, kh 4 / 8 / 16 = 3114 / 3650 / 4027 GCUPS)
+    double step_rows_f64 = 1.0;
+    double f64_row_cost = 2.2;        // FP32 cell rate / FP64 cell rate on full tiles (3716 / 1737 GCUPS, C4)
     double exact_row_cost = 0.9;
+    double lanes8_cost = 1.08;        // 8-lane classes: 3729 against 4027 GCUPS at kh = 16
+    double lanes32_cost = 1.015;
 };
 CostModel default_cost_model();
 // cost[b]: predicted time of batch b (arbitrary unit); read_rescued (may be NULL): 1 where the predictor expects

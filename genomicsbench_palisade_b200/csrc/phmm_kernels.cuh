@@ -142,8 +142,15 @@ __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float 
     P.raw32[oidx] = res;
     // Fast kernel: a sum inside the guard band around MIN_ACCEPTED, or a non-finite one (overflow
     // of the scaled recurrence), is re-decided by the bit-exact FP32 kernel.
-    const bool redo = FAST && (!(res <= 3.402823466e+38f) ||
-                               (P.mode == 0 && res >= P.guard_lo && res < P.guard_hi));
+    // The band is a function of the pair alone (|contracted - unfused| <= ~5 (R + H) ulp relative on an
+    // all-positive recurrence; 8x that, never less than 2^-7), so that a pair's result does not depend on what
+    // else is in the workload or on how a host-buffer call was cut into chunks.
+    bool redo = false;
+    if (FAST) {
+        const float rel = fmaxf(0.0078125f, (float)(rslen + hap_len) * 2.384e-6f);
+        redo = !(res <= 3.402823466e+38f) ||
+               (P.mode == 0 && res >= MIN_ACCEPTED_F * (1.0f - rel) && res < MIN_ACCEPTED_F * (1.0f + rel));
+    }
     if (redo || (P.mode == 0 && res < MIN_ACCEPTED_F)) {
         // :73-75 -- below MIN_ACCEPTED the pair is re-run in FP64 (by the FP64 kernel of the
         // read's class).

@@ -51,6 +51,33 @@ static int scalar_class_of(int rslen)
     return kh <= MAX_KH_SCALAR ? kh : 0;
 }
 
+// Whether a call is planned for latency (PlanOptions::latency = -1: by its size).  A host-buffer call decides once
+// for all of its chunks, so that a pair's result does not depend on how the call was cut.
+int plan_latency(const phmm_flat_batches &fb, const PlanOptions &opt)
+{
+    if (opt.latency >= 0) return opt.latency;
+    // tasks if every read took one warp per pair of haplotypes (~50 us each): below eight per resident warp
+    // the call ends before the throughput plan (long runs, tall tiles, few kernels at once) has filled the
+    // device -- measured on 16 active regions per call: 0.55 ms of FP32 kernels against 0.25.  Not when the
+    // tasks are few but long (kilobase haplotypes): above ~1 ms of device work the throughput plan's shorter
+    // runs fill the device as well and its tall tiles run the cells faster.
+    const int64_t limit = 8 * (int64_t)opt.resident_warps;
+    int64_t t = 0, r = 0, h = 0;
+    double cells = 0;
+    for (int64_t b = 0; b < fb.n_batches && t < limit && cells < 3e9; ++b) {
+        const int nr = std::max(fb.batch_num_reads[b], 0), nh = std::max(fb.batch_num_haps[b], 0);
+        t += (int64_t)nr * ((nh + 1) / 2);
+        if (r + nr <= fb.n_reads && h + nh <= fb.n_haps && fb.read_len && fb.hap_len) {
+            double sr = 0, sh = 0;
+            for (int k = 0; k < nr; ++k) sr += fb.read_len[r + k];
+            for (int k = 0; k < nh; ++k) sh += fb.hap_len[h + k];
+            cells += sr * sh;
+        }
+        r += nr; h += nh;
+    }
+    return (t < limit && cells < 3e9) ? 1 : 0;
+}
+
 int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *plan, std::string *err)
 {
     char msg[256];
@@ -65,16 +92,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
     P = Plan();
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) P.resc_cap[k] = 0;
     PlanOptions opt = opt_in;
-    if (opt.latency < 0) {
-        // tasks if every read took one warp per pair of haplotypes (~50 us each): below eight per resident warp
-        // the call ends before the throughput plan (long runs, tall tiles, few kernels at once) has filled the
-        // device -- measured on 16 active regions per call: 0.55 ms of FP32 kernels against 0.25
-        const int64_t limit = 8 * (int64_t)opt.resident_warps;
-        int64_t t = 0;
-        for (int64_t b = 0; b < fb.n_batches && t < limit; ++b)
-            t += (int64_t)std::max(fb.batch_num_reads[b], 0) * ((std::max(fb.batch_num_haps[b], 0) + 1) / 2);
-        opt.latency = t < limit ? 1 : 0;
-    }
+    if (opt.latency < 0) opt.latency = plan_latency(fb, opt);
     P.latency = opt.latency;
 
     // ---- validate tables, count ---------------------------------------------------------------

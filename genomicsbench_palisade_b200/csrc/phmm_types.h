@@ -123,7 +123,6 @@ struct KernelParams {
     int32_t *resc_count;                 // [MAX_KH_SCALAR + 1] one list per scalar kernel class
     int32_t resc_off[MAX_KH_SCALAR + 1]; // start of each class's list inside resc / guard
     int32_t mode;                        // PHMM_OPT_PRECISION
-    float guard_lo, guard_hi;            // fast kernel: sums in [lo, hi) go to the exact kernel
     Task *guard;                         // guard-band list (fast kernel only)
     int32_t *guard_count;
     T *scratch;                          // multi-pass kernels: per-warp boundary rows

@@ -134,13 +134,11 @@ def test_host_entry_point_pipelines_chunks():
             out2 = eng.compute(fb, out=np.empty(fb.n_pairs))        # arenas reused
             eng.close()
             r = ref.rescued.astype(bool)
+            # the low bits of the fast FP32 kernels depend on the class a read runs in; the plan (throughput or
+            # latency) is decided once per call and the guard band per pair, so the cut into chunks changes nothing
+            assert np.array_equal(out, res[0])
             if fast:
-                # the low bits of the fast FP32 kernels depend on the class a read runs in, and the planner
-                # picks classes by the size of the chunk (small calls: 32 lanes per read); the FP64 classes do not
-                assert np.array_equal(out[r], res[0][r])
                 assert same_or_close(out[~r], ref.out[~r], RTOL_FP32)
-            else:
-                assert np.array_equal(out, res[0])
             assert np.array_equal(out2, out)
             assert st["n_pairs"] == fb.n_pairs and st["n_cells"] == fb.n_cells
             assert st["n_rescued"] == int(ref.rescued.sum())
