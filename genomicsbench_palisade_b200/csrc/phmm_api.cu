@@ -77,7 +77,7 @@ struct phmm_ctx {
     int canary = 0;           // PHMM_CANARY=1: red zones behind every device buffer, checked after each run
     // slot 0 also serves the device-resident workload API; the host-buffer entry points pipeline
     // chunks of batches through all slots (plan + upload of one chunk under the kernels of the others)
-    static const int N_SLOTS = 3;
+    static const int N_SLOTS = 4;
     StreamSet ss[N_SLOTS];
     Arena arena[N_SLOTS];
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
@@ -141,7 +141,8 @@ struct phmm_workload {
 namespace {
 
 // layout of phmm_workload::d_ints
-const int INTS_COUNTER = 0;                       // one queue head per launch, up to 64 launches
+const int INTS_COUNTER = 0;                       // one queue head per launch: [0, MAX_STEP_LAUNCHES) for the step,
+const int MAX_STEP_LAUNCHES = 64 - (MAX_KH_SCALAR + 1);   //   the last MAX_KH_SCALAR + 1 for the bit-exact FP64 re-run of wl_finish
 const int INTS_NTASKS = 64;                       // per FP32 class
 const int INTS_RESC = 128;                        // [MAX_KH_SCALAR + 1]
 const int INTS_GUARD = 128 + 16;
@@ -322,9 +323,16 @@ namespace {
 // A range of whole batches of a phmm_flat_batches and the reads / haplotypes / pairs it spans.
 struct Chunk { int64_t b0, b1, r0, r1, h0, h1, p0, p1; };
 
-// Cuts the batches into consecutive chunks of about `per` cells (0: total / n_chunks clamped to [min_cells, max_cells]).
+// Cuts the batches into consecutive chunks of whole batches.
+//   per > 0: about `per` cells each (PHMM_OPT_CHUNK_CELLS);
+//   per = 0: a schedule that starts the device early and ends the call early -- the first chunk is a 64th of the
+//   work (its plan + upload is all the caller waits for before kernels run), every next one four times the last up
+//   to a third of the work (at most max_cells: device memory), and the last ones halve again, so that what is left
+//   after the final kernel (copy-back of one chunk's results, the tail of its last tasks) is small.  Fewer, larger
+//   chunks in the middle: every chunk has its own phase joins and kernel tails (C2: 6 equal chunks 37.0 ms,
+//   this schedule 36.2; profiles/README.md).
 int split_batches(phmm_ctx *ctx, const phmm_flat_batches *fb, int64_t per, int64_t min_cells, int64_t max_cells,
-                  int n_chunks, bool small_first, std::vector<Chunk> *out)
+                  std::vector<Chunk> *out)
 {
     std::vector<Chunk> &chunks = *out;
     chunks.clear();
@@ -343,20 +351,28 @@ int split_batches(phmm_ctx *ctx, const phmm_flat_batches *fb, int64_t per, int64
         total += cells[b];
         r += nr; h += nh;
     }
-    if (per <= 0) per = std::max<int64_t>(min_cells, std::min<int64_t>(max_cells, total / n_chunks + 1));
+    static const struct Sched { double first = 64, growth = 4, cap = 3, tail = 4, floor = 4e9; Sched() {
+        if (const char *e = getenv("PHMM_CHUNK_SCHED")) sscanf(e, "%lf,%lf,%lf,%lf,%lf", &first, &growth, &cap, &tail, &floor); } } sched;
+    const double cap = std::max<double>((double)min_cells, std::min<double>((double)max_cells, total / sched.cap));
+    double want = per > 0 ? (double)per : std::max<double>(total / sched.first, (double)min_cells / 4);
     Chunk c{0, 0, 0, 0, 0, 0, 0, 0};
-    int64_t acc = 0, p = 0;
+    int64_t acc = 0, p = 0, done = 0;
     r = 0; h = 0;
     for (int64_t b = 0; b < fb->n_batches; ++b) {
         const int nr = fb->batch_num_reads[b], nh = fb->batch_num_haps[b];
         acc += cells[b];
         r += nr; h += nh; p += (int64_t)nr * nh;
-        const int64_t want = (small_first && chunks.empty()) ? per / 2 : per;
         if (acc >= want || b == fb->n_batches - 1) {
             c.b1 = b + 1; c.r1 = r; c.h1 = h; c.p1 = p;
             chunks.push_back(c);
             c = Chunk{b + 1, b + 1, r, r, h, h, p, p};
+            done += acc;
             acc = 0;
+            if (per <= 0) {
+                const double left = (double)(total - done);
+                want = std::min(cap, want * sched.growth);
+                if (left < 2 * want) want = left > std::max(cap / sched.tail, sched.floor) ? left / 2 : left;      // the call is ending: halve
+            }
         }
     }
     if (chunks.empty()) chunks.push_back(Chunk{0, 0, 0, 0, 0, 0, 0, 0});
@@ -422,7 +438,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     Plan &P = w->plan;
     w->n_pairs = P.n_pairs;
     w->n_cells = P.n_cells;
-    if (P.classes.size() > 60) { ctx->error = "too many kernel classes"; delete w; return PHMM_ERR_ARG; }
+    if ((int)P.classes.size() + 2 * (MAX_KH_SCALAR + 1) > MAX_STEP_LAUNCHES) { ctx->error = "too many kernel classes"; delete w; return PHMM_ERR_ARG; }
 
     auto fail = [&](int code) { phmm_workload_destroy(w); return code; };
     if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->error = "cudaSetDevice failed"; return fail(PHMM_ERR_CUDA); }
@@ -697,7 +713,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     for (size_t c = 0; c < w->classes.size(); ++c) {
         const ClassDev &cd = w->classes[c];
         if (cd.ntasks == 0) continue;
-        if (counter_slot >= 60) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
+        if (counter_slot >= MAX_STEP_LAUNCHES) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
         CUDA_TRY(ctx, side_stream(&ks));
         if (mode == 2) {
             KernelF64 k = cd.kc.longr ? lookup_f64_long(fast64) : lookup_f64(cd.kc.kh, fast64);
@@ -726,6 +742,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
         CUDA_TRY(ctx, fork());
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (w->resc_cap[kh] == 0) continue;
+            if (counter_slot >= MAX_STEP_LAUNCHES) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
             CUDA_TRY(ctx, side_stream(&ks));
             KernelF32 k = kh ? lookup_f32_l32_f0(kh) : lookup_f32_long(false);
             pf.tasks = w->d_guard + w->resc_off[kh];
@@ -745,6 +762,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
         CUDA_TRY(ctx, fork());
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (w->resc_cap[kh] == 0) continue;
+            if (counter_slot >= MAX_STEP_LAUNCHES) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
             CUDA_TRY(ctx, side_stream(&ks));
             KernelF64 k = kh ? lookup_f64(kh, fast64) : lookup_f64_long(fast64);
             pd.tasks = w->d_resc + w->resc_off[kh];
@@ -765,11 +783,11 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     // (launched by wl_finish when the counters say so: the common case pays nothing)
     if (mode != 1 && fast64) {
         pd.guard = nullptr;
-        counter_slot = 48;                 // queue heads zeroed at the start of the step and not used by it
+        counter_slot = MAX_STEP_LAUNCHES;  // queue heads reserved for this re-run: zeroed at the start of the step, never handed out by it
         CUDA_TRY(ctx, fork());
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (fallback64[kh] == 0) continue;
-            if (counter_slot >= 60) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
+            if (counter_slot >= 64) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
             CUDA_TRY(ctx, side_stream(&ks));
             KernelF64 k = kh ? lookup_f64(kh, false) : lookup_f64_long(false);
             pd.tasks = w->d_guard + w->resc_off[kh];
@@ -873,11 +891,7 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
     static const bool trace = getenv("PHMM_TRACE") != nullptr;
     std::vector<Chunk> chunks;
     {
-        // default: a fifth of the work per chunk, between 4e9 and 4e10 cells (1 to 10 ms of kernels:
-        // smaller chunks run the device less efficiently -- every chunk has its own phase joins and
-        // kernel tails; measured on C2: 6e9 40.3 ms, 1.2e10 38.5, 2e10 37.7, 4e10 37.2 -- larger ones
-        // expose more of the first plan + upload); the first one half that size so the device starts early
-        int rc0 = split_batches(ctx, fb, ctx->chunk_cells, 4000000000ll, 40000000000ll, 5, true, &chunks);
+        int rc0 = split_batches(ctx, fb, ctx->chunk_cells, 4000000000ll, 40000000000ll, &chunks);
         if (rc0 != PHMM_OK) return rc0;
     }
     if (chunks.back().p1 > 0 && !out) { ctx->error = "NULL output"; return PHMM_ERR_ARG; }
@@ -916,41 +930,62 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         wl[slot] = nullptr;
         return PHMM_OK;
     };
-    // A planner thread runs ahead of the loop below: with many small batches (active regions) planning a
-    // chunk takes as long as its kernels, and the loop's own time is better spent on uploads and launches.
+    // Planner threads run ahead of the loop below: with many small batches (active regions, C1) planning a chunk
+    // takes as long as its kernels, the chunk schedule grows fourfold per chunk while the device only just keeps up
+    // with one planner, and the loop's own time is better spent on uploads and launches.  Chunks are planned
+    // concurrently, at most six ahead of the one being launched (a plan holds the chunk's task lists).
     struct PlanJob { Plan plan; std::string err; int rc = PHMM_OK; bool done = false; };
     std::vector<PlanJob> jobs(chunks.size());
     std::mutex pmu;
     std::condition_variable pcv;
     bool pstop = false;
+    size_t next_job = 0, consumed = 0;
     PlanOptions popt = plan_options(ctx);
     popt.latency = plan_latency(*fb, popt);        // one decision for the whole call, not one per chunk
-    std::thread planner;
-    if (chunks.size() > 1)
-        planner = std::thread([&]() {
-            for (size_t j = 0; j < chunks.size(); ++j) {
-                { std::lock_guard<std::mutex> lk(pmu); if (pstop) return; }
+    static const int n_planners_env = getenv("PHMM_PLANNERS") ? atoi(getenv("PHMM_PLANNERS")) : 0;
+    const int n_planners = chunks.size() > 1
+        ? std::max(1, std::min<int>({n_planners_env > 0 ? n_planners_env : 3, (int)chunks.size(),
+                                     (int)std::max(1u, std::thread::hardware_concurrency() / 2)}))
+        : 0;
+    std::vector<std::thread> planners;
+    for (int k = 0; k < n_planners; ++k)
+        planners.emplace_back([&]() {
+            for (;;) {
+                size_t j;
+                {
+                    std::unique_lock<std::mutex> lk(pmu);
+                    pcv.wait(lk, [&]() { return pstop || next_job >= chunks.size() || next_job < consumed + 6; });
+                    if (pstop || next_job >= chunks.size()) return;
+                    j = next_job++;
+                }
                 const phmm_flat_batches sub = sub_batches(fb, chunks[j]);
                 const int prc = build_plan(sub, popt, &jobs[j].plan, &jobs[j].err);
-                { std::lock_guard<std::mutex> lk(pmu); jobs[j].rc = prc; jobs[j].done = true; }
+                { std::lock_guard<std::mutex> lk(pmu); jobs[j].rc = prc; jobs[j].done = true; if (prc != PHMM_OK) pstop = true; }
                 pcv.notify_all();
                 if (prc != PHMM_OK) return;
             }
         });
     struct PlannerGuard {
-        std::thread &t; std::mutex &m; bool &stop;
-        ~PlannerGuard() { { std::lock_guard<std::mutex> lk(m); stop = true; } if (t.joinable()) t.join(); }
-    } planner_guard{planner, pmu, pstop};
+        std::vector<std::thread> &t; std::mutex &m; std::condition_variable &cv; bool &stop;
+        ~PlannerGuard()
+        {
+            { std::lock_guard<std::mutex> lk(m); stop = true; }
+            cv.notify_all();
+            for (std::thread &th : t) if (th.joinable()) th.join();
+        }
+    } planner_guard{planners, pmu, pcv, pstop};
     for (size_t j = 0; j < chunks.size() && rc == PHMM_OK; ++j) {
         const int slot = (int)(j % phmm_ctx::N_SLOTS);
         // the slot's arena must be idle: wait for the chunk that used it and fetch its results
         if (wl[slot]) rc = retire(j - phmm_ctx::N_SLOTS);
         if (rc != PHMM_OK) break;
         Plan *prebuilt = nullptr;
-        if (planner.joinable()) {
+        if (n_planners > 0) {
             std::unique_lock<std::mutex> lk(pmu);
             pcv.wait(lk, [&]() { return jobs[j].done; });
             if (jobs[j].rc != PHMM_OK) { ctx->error = jobs[j].err; rc = jobs[j].rc; break; }
+            consumed = j + 1;
+            pcv.notify_all();
             prebuilt = &jobs[j].plan;
         }
         const Chunk &c = chunks[j];
@@ -982,6 +1017,22 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
         stats->ms_h2d = (float)(t_first_launch - t_begin);   // exposed: plan + upload of the first chunk
         stats->ms_d2h = (float)ms_d2h;                       // host time in result copies (mostly overlapped)
     }
+    return PHMM_OK;
+}
+
+extern "C" int phmm_host_register(phmm_ctx *ctx, void *ptr, size_t bytes)
+{
+    if (!ctx || !ptr || bytes == 0) return PHMM_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return PHMM_OK;
+}
+
+extern "C" int phmm_host_unregister(phmm_ctx *ctx, void *ptr)
+{
+    if (!ctx || !ptr) return PHMM_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaHostUnregister(ptr));
     return PHMM_OK;
 }
 

@@ -179,6 +179,11 @@ extern "C" int phmm_cache_open(const char *path, phmm_parsed **out, char *err, s
     if (fnv1a64(tab, sizeof tab) != hd.table_sum) return bad("section table checksum mismatch");
     if (hd.n_batches < 0 || hd.n_reads < 0 || hd.n_haps < 0 || hd.read_pool_bytes < 0 || hd.hap_pool_bytes < 0)
         return bad("negative count");
+    // counts are bounded by the file length BEFORE they are multiplied: a crafted n_reads = 2^61 would wrap to a
+    // small section size, pass the bounds test below and send the table walks far past the mapping
+    if ((uint64_t)hd.n_batches > len / 4 || (uint64_t)hd.n_reads > len / 8 || (uint64_t)hd.n_haps > len / 8 ||
+        (uint64_t)hd.read_pool_bytes > len || (uint64_t)hd.hap_pool_bytes > len)
+        return bad("count larger than the file");
     const uint64_t want[N_SECTIONS] = {
         (uint64_t)hd.n_batches * 4, (uint64_t)hd.n_batches * 4, (uint64_t)hd.n_reads * 4, (uint64_t)hd.n_reads * 8,
         (uint64_t)hd.read_pool_bytes, (uint64_t)hd.read_pool_bytes, (uint64_t)hd.read_pool_bytes,
@@ -210,10 +215,12 @@ extern "C" int phmm_cache_open(const char *path, phmm_parsed **out, char *err, s
     }
     if (sr != v.n_reads || sh != v.n_haps) return bad("batch tables do not add up");
     for (int64_t r = 0; r < v.n_reads; ++r)
-        if (v.read_len[r] <= 0 || v.read_off[r] < 0 || v.read_off[r] + v.read_len[r] > hd.read_pool_bytes)
+        if (v.read_len[r] <= 0 || v.read_off[r] < 0 || v.read_len[r] > hd.read_pool_bytes ||
+            v.read_off[r] > hd.read_pool_bytes - v.read_len[r])
             return bad("read outside its pool");
     for (int64_t h = 0; h < v.n_haps; ++h)
-        if (v.hap_len[h] <= 0 || v.hap_off[h] < 0 || v.hap_off[h] + v.hap_len[h] > hd.hap_pool_bytes)
+        if (v.hap_len[h] <= 0 || v.hap_off[h] < 0 || v.hap_len[h] > hd.hap_pool_bytes ||
+            v.hap_off[h] > hd.hap_pool_bytes - v.hap_len[h])
             return bad("haplotype outside its pool");
     *out = p;
     return PHMM_OK;

@@ -126,7 +126,14 @@ extern "C" int phmm_gatk_init(int device, int use_double, int max_threads, int u
     if (rc != PHMM_OK) { g_gatk_create_error = phmm_last_error(nullptr); return rc; }
     // computeLikelihoodsNative's policy: FP32 then FP64 below MIN_ACCEPTED, or FP64 only
     phmm_set_option(ctx, PHMM_OPT_PRECISION, use_double ? 2 : 0);
-    phmm_set_option(ctx, PHMM_OPT_FP32_KERNEL, 1);
+    // Bit-exact kernels by default: a variant caller expects a pair's likelihood not to depend on which other
+    // regions share the call, and the low bits of the fast FP32 kernels depend on the kernel class a read runs in,
+    // which the planner picks by the size of the call.  PHMM_GATK_FAST=1, or phmm_set_option(phmm_gatk_context(g),
+    // PHMM_OPT_FP32_KERNEL / PHMM_OPT_FP64_KERNEL, 1), opts into the fast ones (same rescue set, |rel err| ~1e-6).
+    const char *fast_env = getenv("PHMM_GATK_FAST");
+    const int fast = (fast_env && atoi(fast_env) != 0) ? 1 : 0;
+    phmm_set_option(ctx, PHMM_OPT_FP32_KERNEL, fast);
+    phmm_set_option(ctx, PHMM_OPT_FP64_KERNEL, fast);
     phmm_gatk *g = new phmm_gatk();
     g->ctx = ctx;
     g->use_double = use_double ? 1 : 0;

@@ -56,7 +56,7 @@ class CTestcase(C.Structure):
 
 EXPORTS = ["phmm_abi_version", "phmm_device_count", "phmm_create", "phmm_destroy", "phmm_set_option",
            "phmm_get_option", "phmm_last_error", "phmm_compute_pairs", "phmm_compute_batches",
-           "phmm_compute_flat", "phmm_workload_create", "phmm_workload_run", "phmm_workload_results",
+           "phmm_compute_flat", "phmm_host_register", "phmm_host_unregister", "phmm_workload_create", "phmm_workload_run", "phmm_workload_results",
            "phmm_workload_destroy", "phmm_partition_lpt", "phmm_batch_costs", "phmm_parse_file", "phmm_parse_buffer",
            "phmm_parsed_batches", "phmm_parsed_free", "phmm_microbench", "phmm_get_tables",
            "phmm_plan_summary", "phmm_cache_write", "phmm_cache_open", "phmm_gatk_init",
@@ -206,13 +206,19 @@ class GatkPairHMM:
     phmm_gatk_*.  A read is a 5-tuple of bytes objects (readBases, readQuals, insertionGOP,
     deletionGOP, overallGCP) with raw Phred values, a haplotype a bytes object."""
 
-    def __init__(self, device: int = 0, use_double: bool = False, max_threads: int = 1):
+    def __init__(self, device: int = 0, use_double: bool = False, max_threads: int = 1, fast=None):
+        """fast: None = the library's default (bit-exact kernels unless PHMM_GATK_FAST=1), True / False = set the
+        kernels through the underlying context as a C caller would."""
         self.lib = load_library()
         self._h = C.c_void_p()
         rc = self.lib.phmm_gatk_init(C.c_int(device), C.c_int(int(use_double)), C.c_int(max_threads),
                                      C.c_int(0), C.byref(self._h))
         if rc:
             raise PhmmError(rc, (self.lib.phmm_gatk_last_error(None) or b"").decode())
+        if fast is not None:
+            ctx = C.c_void_p(self.lib.phmm_gatk_context(self._h))
+            for opt in (OPT_FP32_KERNEL, OPT_FP64_KERNEL):
+                self._check(self.lib.phmm_set_option(ctx, C.c_int(opt), C.c_int64(int(bool(fast)))))
 
     def _check(self, rc):
         if rc:
@@ -400,6 +406,17 @@ class PairHMM:
         st = CStats()
         self._check(self.lib.phmm_compute_flat(self._h, C.byref(keep.c), _ptr(out), C.byref(st)))
         return (out, st.as_dict()) if stats else out
+
+    def pin(self, *arrays):
+        """phmm_host_register on caller-owned numpy arrays that live across many calls."""
+        for a in arrays:
+            if a is not None and a.nbytes:
+                self._check(self.lib.phmm_host_register(self._h, C.c_void_p(a.ctypes.data), C.c_size_t(a.nbytes)))
+
+    def unpin(self, *arrays):
+        for a in arrays:
+            if a is not None and a.nbytes:
+                self._check(self.lib.phmm_host_unregister(self._h, C.c_void_p(a.ctypes.data)))
 
     def compute_pairs(self, fb: FlatBatches):
         """Through the reference's own argument list: a testcase[] of pointers (computelikelihoodsboth)."""

@@ -162,6 +162,14 @@ int phmm_compute_pairs(phmm_ctx *ctx, const phmm_testcase *pairs, double *out, i
 int phmm_compute_batches(phmm_ctx *ctx, const phmm_batch *batches, int64_t n_batches);
 int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, double *out, phmm_stats *stats);
 
+/* Optional: page-lock caller-owned buffers that live across many calls (the pools of phmm_flat_batches, the results
+ * array), so that the library's copies run as asynchronous DMA at full PCIe / NVLink-C2C rate instead of being staged
+ * through the driver's bounce buffer (cudaHostRegister behind a plain-pointer interface: a cgo / JNI / ctypes caller
+ * has no CUDA headers).  The reference has no counterpart -- its buffers never leave the host
+ * (PairHMMUnitTest_orig.cpp:246 allocates them with _mm_malloc).  Unregister before freeing the buffer. */
+int phmm_host_register(phmm_ctx *ctx, void *ptr, size_t bytes);
+int phmm_host_unregister(phmm_ctx *ctx, void *ptr);
+
 /* ---- device-resident workloads -------------------------------------------------------------- */
 /* Plan (kernel classes, haplotype-stream segments, LPT-ordered warp tasks) and upload. */
 int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, phmm_workload **w);
@@ -222,6 +230,14 @@ int phmm_cache_open(const char *path, phmm_parsed **out, char *err, size_t err_l
  *                 (IntelPairHmm.cc:123-124: result_float = 0.0f < MIN_ACCEPTED).
  *   max_threads : host threads of the reference's OpenMP loop; accepted and ignored.
  *   use_fpga    : the reference's FPGA hook (shacc_pairhmm::calculate, always false); must be 0.
+ * Kernels: the bit-exact ones by default (raw FP32 / FP64 sums identical to the reference's AVX code, so a pair's
+ * likelihood does not depend on which other regions share the call).  The fast kernels are an opt-in
+ * (environment PHMM_GATK_FAST=1, or phmm_set_option(phmm_gatk_context(g), PHMM_OPT_FP32_KERNEL, 1)): same
+ * FP64-rescue set, FP32-path likelihoods within ~1e-6 relative, but their low bits depend on the kernel class a
+ * read runs in, which the planner picks by the size of the call (one region: 32 lanes per read).
+ * log10: the returned value goes through the device's log10f / log10 (documented maximum error 2 ulp / 1 ulp)
+ * where the reference calls glibc's; "bit-exact" in this library refers to the raw sums, the returned log10
+ * likelihoods agree within those ulps (tests hold them to 1e-4 / 1e-9 relative, BASELINE.json's bars).
  * FTZ: initNative turns on x86 flush-to-zero (:66-70).  The kernels here honour denormals, which
  * changes a result only when an FP32 intermediate falls below 2^-126 (the pair is then far below
  * MIN_ACCEPTED = 1e-28f or the lost term is < 2^-50 of the sum) or an FP64 intermediate below

@@ -334,8 +334,8 @@ def _regions(fb):
 
 def test_gatk_shaped_api():
     # IntelPairHmm.computeLikelihoods (IntelPairHmm.cc:103-156): all reads x all haplotypes, read-major
-    for use_double in (False, True):
-        g = phmm.GatkPairHMM(use_double=use_double)
+    for use_double, fast in ((False, None), (True, None), (False, True)):
+        g = phmm.GatkPairHMM(use_double=use_double, fast=fast)
         # the reference's known-answer test through this entry (PairHmmUnitTest.java:42-55): raw
         # (un-normalised) '+' bytes, tolerance 1e-5
         kat = g.compute_likelihoods([(b"ACGT", b"++++", b"++++", b"++++", b"++++")], [b"ACGT"])
@@ -351,8 +351,11 @@ def test_gatk_shaped_api():
         else:
             r = ref.rescued.astype(bool)
             assert r.any() and (~r).any()
-            # FP64 classes do not depend on the plan; the low bits of the fast FP32 kernels do (a single region
-            # is planned for latency: 32 lanes per read)
+            # default = bit-exact kernels: a pair's likelihood does not depend on what shares its call.  The fast
+            # kernels are an opt-in: FP64 classes do not depend on the plan; the low bits of the fast FP32 kernels
+            # do (a single region is planned for latency: 32 lanes per read)
+            if not fast:
+                assert np.array_equal(one_by_one, together)
             assert np.array_equal(one_by_one[r], together[r])
             assert same_or_close(one_by_one[~r], ref.out[~r], RTOL_FP32)
             assert same_or_close(together[~r], ref.out[~r], RTOL_FP32) and same_or_close(together[r], ref.out[r], RTOL_FP64)

@@ -148,6 +148,34 @@ def test_binary_cache_round_trip_and_corruption(tmp_path):
     open(path, "wb").write(raw[:len(raw) // 2])
     with pytest.raises(phmm.PhmmError):
         phmm.cache_open(path)
+    # a crafted header whose counts wrap when multiplied (n_reads = 2^61 -> 0 bytes of read_len) together with a
+    # section table rewritten to match (the FNV sums are no integrity boundary: an attacker recomputes them)
+    import struct
+
+    def fnv(b):
+        h, k = 0xcbf29ce484222325, 0
+        while k + 8 <= len(b):
+            h = ((h ^ int.from_bytes(b[k:k + 8], "little")) * 0x100000001b3) & (2 ** 64 - 1)
+            k += 8
+        for x in b[k:]:
+            h = ((h ^ x) * 0x100000001b3) & (2 ** 64 - 1)
+        return h
+
+    evil = bytearray(raw)
+    struct.pack_into("<q", evil, 24, 2 ** 61)                       # Header::n_reads
+    tab = bytearray(evil[128:128 + 12 * 24])
+    for sec in (2, 3):                                              # read_len, read_off: sizes wrap to 0
+        off, _, _ = struct.unpack_from("<QQQ", tab, sec * 24)
+        struct.pack_into("<QQQ", tab, sec * 24, off, 0, fnv(b""))
+    evil[128:128 + 12 * 24] = tab
+    if fnv(bytes(raw[128:128 + 12 * 24])) == struct.unpack_from("<Q", raw, 56)[0]:     # the test's FNV is the file's
+        struct.pack_into("<Q", evil, 56, fnv(bytes(tab)))
+        open(path, "wb").write(evil)
+        with pytest.raises(phmm.PhmmError) as e:
+            phmm.cache_open(path)
+        assert e.value.code == 6 and "count larger than the file" in str(e.value)
+    else:
+        raise AssertionError("test FNV does not reproduce the file's table checksum")
     with pytest.raises(phmm.PhmmError) as e:
         phmm.cache_open(str(tmp_path / "missing"))
     assert e.value.code == 7

@@ -44,6 +44,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--regions", type=int, default=1024)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--kernels", default="exact", choices=["exact", "fast"],
+                    help="exact = the entry's default (bit-exact kernels); fast = the opt-in (PHMM_OPT_FP32/FP64_KERNEL 1)")
     a = ap.parse_args()
     # active regions: 20-120 reads of 100-250 bp x 2-12 haplotypes of 200-500 bp
     fb = synth.generic(synth.SEED0 + 60, a.regions, (20, 120), (2, 12), (100, 250), (200, 500), foreign_frac=0.03,
@@ -51,8 +53,8 @@ def main():
     regs = regions_of(fb)
     cells = fb.batch_cells.astype(np.int64)
     out = {"metric": "GATK-shaped batch API (phmm_gatk_*), end to end", "regions": len(regs), "pairs": fb.n_pairs,
-           "cells": int(cells.sum()), "mean_pairs_per_region": fb.n_pairs / len(regs), "groups": []}
-    g = phmm.GatkPairHMM()
+           "cells": int(cells.sum()), "mean_pairs_per_region": fb.n_pairs / len(regs), "kernels": a.kernels, "groups": []}
+    g = phmm.GatkPairHMM(fast=(a.kernels == "fast"))
     # ctypes marshalling of thousands of small byte strings is Python time, not library time: build the C
     # holder arrays once per group outside the timed region
     import ctypes as C
