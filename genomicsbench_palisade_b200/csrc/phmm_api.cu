@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <condition_variable>
+#include <deque>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -95,6 +96,16 @@ struct phmm_ctx {
     std::mutex mu;     // the legacy symbols may be entered from several OpenMP threads
     // resident blocks per SM of each kernel (asked of the runtime once, not at every launch)
     std::unordered_map<const void *, int> blocks_per_sm;
+    // phmm_submit_pairs / phmm_wait: submissions in flight, oldest first
+    struct Inflight {
+        struct Scatter { double *out; int64_t p0, n; };
+        phmm_workload *w = nullptr;
+        int slot = 0;
+        int64_t ticket = 0;
+        std::vector<Scatter> scatter;
+    };
+    std::deque<Inflight> inflight;
+    int64_t next_ticket = 0;
 };
 
 struct ClassDev {
@@ -262,6 +273,11 @@ extern "C" int phmm_destroy(phmm_ctx *ctx)
 {
     if (!ctx) return PHMM_OK;
     cudaSetDevice(ctx->device);
+    if (!ctx->inflight.empty()) {
+        cudaDeviceSynchronize();
+        for (phmm_ctx::Inflight &f : ctx->inflight) phmm_workload_destroy(f.w);
+        ctx->inflight.clear();
+    }
     cudaFree(ctx->d_ph2pr_f); cudaFree(ctx->d_ph2pr_d); cudaFree(ctx->d_mm_f); cudaFree(ctx->d_mm_d);
     cudaFree(ctx->d_bench);
     for (int k = 0; k < phmm_ctx::N_SLOTS; ++k) {
@@ -1139,11 +1155,9 @@ extern "C" int phmm_compute_batches(phmm_ctx *ctx, const phmm_batch *batches, in
 // into per-read / per-haplotype strings (PairHMMUnitTest_orig.cpp:284-297); consecutive pairs
 // with the same `rs` pointer become one read's haplotype list, and consecutive reads with the
 // same haplotype pointer list fold back into the reads x haplotypes batch they came from.
-extern "C" int phmm_compute_pairs(phmm_ctx *ctx, const phmm_testcase *tc, double *out, int64_t n)
+// Appends the batches of one testcase array to `fbld` (pairs keep their order: batch-major, read-major).
+static int append_testcases(phmm_ctx *ctx, FlatBuilder &fbld, const phmm_testcase *tc, int64_t n)
 {
-    if (!ctx || n < 0 || (n && (!tc || !out))) return PHMM_ERR_ARG;
-    if (n == 0) return PHMM_OK;
-    FlatBuilder fbld;
     ParsedBatches &b = fbld.b;
     int64_t k = 0;
     int64_t prev_first = -1, prev_nh = 0;      // pair index / size of the previous read's hap list
@@ -1178,8 +1192,169 @@ extern "C" int phmm_compute_pairs(phmm_ctx *ctx, const phmm_testcase *tc, double
         prev_nh = nh;
         k = k1;
     }
-    b.finish();
-    return phmm_compute_flat(ctx, &b.view, out, nullptr);
+    return PHMM_OK;
+}
+
+extern "C" int phmm_compute_pairs(phmm_ctx *ctx, const phmm_testcase *tc, double *out, int64_t n)
+{
+    if (!ctx || n < 0 || (n && (!tc || !out))) return PHMM_ERR_ARG;
+    if (n == 0) return PHMM_OK;
+    FlatBuilder fbld;
+    int rc = append_testcases(ctx, fbld, tc, n);
+    if (rc != PHMM_OK) return rc;
+    fbld.b.finish();
+    return phmm_compute_flat(ctx, &fbld.b.view, out, nullptr);
+}
+
+// testcase[] -> flat batches owned by the returned handle (phmm_parsed_batches / phmm_parsed_free): the per-pair part
+// of a legacy call, done by the calling thread so that a dispatcher only has to merge and launch.
+extern "C" int phmm_flatten_pairs(const phmm_testcase *tc, int64_t n, phmm_parsed **out, char *err, size_t err_len)
+{
+    if (!out || n < 0 || (n && !tc)) return PHMM_ERR_ARG;
+    *out = nullptr;
+    phmm_ctx tmp;                       // only its error string is used
+    FlatBuilder fbld;
+    const int rc = append_testcases(&tmp, fbld, tc, n);
+    if (rc != PHMM_OK) { if (err && err_len) snprintf(err, err_len, "%s", tmp.error.c_str()); return rc; }
+    phmm_parsed *p = new phmm_parsed();
+    p->b = std::move(fbld.b);
+    p->b.finish();
+    *out = p;
+    return PHMM_OK;
+}
+
+// ============================================================================================
+// asynchronous host-buffer calls: several callers' batches in one planned chunk
+// ============================================================================================
+// phmm_submit_pairs merges the requests into one set of batches, plans it, queues its uploads and kernels in a
+// free pipeline slot and returns; phmm_wait copies every request's results into its own array.  Up to N_SLOTS
+// submissions are in flight; a submit that finds no free slot retires the oldest first.
+extern "C" int phmm_wait(phmm_ctx *ctx, int64_t ticket)
+{
+    if (!ctx) return PHMM_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    while (!ctx->inflight.empty() && ctx->inflight.front().ticket <= ticket) {
+        phmm_ctx::Inflight f = std::move(ctx->inflight.front());
+        ctx->inflight.pop_front();
+        StreamSet &ss = ctx->ss[f.slot];
+        int rc = wl_finish(ctx, f.w, ss, nullptr);
+        if (rc == PHMM_OK) {
+            for (const phmm_ctx::Inflight::Scatter &sc : f.scatter)
+                if (sc.n > 0 && cudaMemcpyAsync(sc.out, f.w->d_out + sc.p0, (size_t)sc.n * sizeof(double), cudaMemcpyDeviceToHost,
+                                                ss.main) != cudaSuccess) { ctx->error = "result copy failed"; rc = PHMM_ERR_CUDA; break; }
+            if (rc == PHMM_OK && cudaStreamSynchronize(ss.main) != cudaSuccess) { ctx->error = "result copy failed"; rc = PHMM_ERR_CUDA; }
+        }
+        phmm_workload_destroy(f.w);
+        if (rc != PHMM_OK) return rc;
+    }
+    return PHMM_OK;
+}
+
+// Queues one merged set of batches (owned by the caller of this helper until it returns) in a free slot.
+static int submit_merged(phmm_ctx *ctx, const phmm_flat_batches &view, phmm_ctx::Inflight &f, int64_t *ticket)
+{
+    f.ticket = ++ctx->next_ticket;
+    f.slot = (int)(f.ticket % phmm_ctx::N_SLOTS);
+    // the slot's arena and streams must be idle
+    for (const phmm_ctx::Inflight &g : ctx->inflight)
+        if (g.slot == f.slot) { int rc = phmm_wait(ctx, g.ticket); if (rc != PHMM_OK) return rc; break; }
+    PlanOptions popt = plan_options(ctx);
+    popt.latency = plan_latency(view, popt);
+    StreamSet &ss = ctx->ss[f.slot];
+    int rc = wl_create(ctx, &view, &ctx->arena[f.slot], ctx->copy_in, &f.w, nullptr, &popt);
+    if (rc != PHMM_OK) return rc;
+    if (cudaEventRecord(ss.ev_uploaded, ctx->copy_in) != cudaSuccess) { ctx->error = "cudaEventRecord failed"; phmm_workload_destroy(f.w); return PHMM_ERR_CUDA; }
+    rc = wl_launch(ctx, f.w, ss, ss.ev_uploaded);
+    if (rc != PHMM_OK) { cudaDeviceSynchronize(); phmm_workload_destroy(f.w); return rc; }
+    *ticket = f.ticket;
+    ctx->inflight.push_back(std::move(f));
+    return PHMM_OK;
+}
+
+extern "C" int phmm_submit_flat(phmm_ctx *ctx, const phmm_flat_request *reqs, int n_reqs, int64_t *ticket)
+{
+    if (!ctx || n_reqs < 0 || (n_reqs && !reqs) || !ticket) return PHMM_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    phmm_ctx::Inflight f;
+    if (n_reqs == 1 && reqs[0].batches) {          // nothing to merge
+        const phmm_flat_batches &v = *reqs[0].batches;
+        int64_t np = 0;
+        for (int64_t b = 0; b < v.n_batches; ++b) np += (int64_t)v.batch_num_reads[b] * v.batch_num_haps[b];
+        if (np && !reqs[0].out) { ctx->error = "NULL output"; return PHMM_ERR_ARG; }
+        f.scatter.push_back({reqs[0].out, 0, np});
+        return submit_merged(ctx, v, f, ticket);
+    }
+    // concatenate: tables appended, pools copied back to back, offsets rebased
+    ParsedBatches m;
+    int64_t p = 0;
+    size_t tot_r = 0, tot_h = 0, tot_nr = 0, tot_nh = 0, tot_nb = 0;
+    for (int k = 0; k < n_reqs; ++k) {
+        const phmm_flat_batches *v = reqs[k].batches;
+        if (!v || v->n_batches < 0 || v->n_reads < 0 || v->n_haps < 0) { ctx->error = "malformed request"; return PHMM_ERR_ARG; }
+        tot_nb += (size_t)v->n_batches; tot_nr += (size_t)v->n_reads; tot_nh += (size_t)v->n_haps;
+        for (int64_t r = 0; r < v->n_reads; ++r) tot_r += (size_t)std::max(v->read_len[r], 0);
+        for (int64_t h = 0; h < v->n_haps; ++h) tot_h += (size_t)std::max(v->hap_len[h], 0);
+    }
+    m.batch_num_reads.reserve(tot_nb); m.batch_num_haps.reserve(tot_nb);
+    m.read_len.reserve(tot_nr); m.read_off.reserve(tot_nr); m.hap_len.reserve(tot_nh); m.hap_off.reserve(tot_nh);
+    m.rs.resize(tot_r); m.q.resize(tot_r); m.i.resize(tot_r); m.d.resize(tot_r); m.c.resize(tot_r); m.hap.resize(tot_h);
+    size_t at_r = 0, at_h = 0;
+    for (int k = 0; k < n_reqs; ++k) {
+        const phmm_flat_batches &v = *reqs[k].batches;
+        int64_t np = 0;
+        for (int64_t b = 0; b < v.n_batches; ++b) {
+            if (v.batch_num_reads[b] < 0 || v.batch_num_haps[b] < 0) { ctx->error = "negative batch size"; return PHMM_ERR_ARG; }
+            m.batch_num_reads.push_back(v.batch_num_reads[b]);
+            m.batch_num_haps.push_back(v.batch_num_haps[b]);
+            np += (int64_t)v.batch_num_reads[b] * v.batch_num_haps[b];
+        }
+        if (np && !reqs[k].out) { ctx->error = "NULL output"; return PHMM_ERR_ARG; }
+        for (int64_t r = 0; r < v.n_reads; ++r) {
+            const int len = v.read_len[r];
+            if (len <= 0) { ctx->error = "read of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+            if (v.read_off[r] < 0) { ctx->error = "negative read offset"; return PHMM_ERR_ARG; }
+            m.read_len.push_back(len);
+            m.read_off.push_back((int64_t)at_r);
+            memcpy(m.rs.data() + at_r, v.rs + v.read_off[r], (size_t)len);
+            memcpy(m.q.data() + at_r, v.q + v.read_off[r], (size_t)len);
+            memcpy(m.i.data() + at_r, v.i + v.read_off[r], (size_t)len);
+            memcpy(m.d.data() + at_r, v.d + v.read_off[r], (size_t)len);
+            memcpy(m.c.data() + at_r, v.c + v.read_off[r], (size_t)len);
+            at_r += (size_t)len;
+        }
+        for (int64_t h = 0; h < v.n_haps; ++h) {
+            const int len = v.hap_len[h];
+            if (len <= 0) { ctx->error = "haplotype of length <= 0"; return PHMM_ERR_EMPTY_SEQ; }
+            if (v.hap_off[h] < 0) { ctx->error = "negative haplotype offset"; return PHMM_ERR_ARG; }
+            m.hap_len.push_back(len);
+            m.hap_off.push_back((int64_t)at_h);
+            memcpy(m.hap.data() + at_h, v.hap + v.hap_off[h], (size_t)len);
+            at_h += (size_t)len;
+        }
+        f.scatter.push_back({reqs[k].out, p, np});
+        p += np;
+    }
+    m.finish();
+    return submit_merged(ctx, m.view, f, ticket);
+}
+
+extern "C" int phmm_submit_pairs(phmm_ctx *ctx, const phmm_pairs_request *reqs, int n_reqs, int64_t *ticket)
+{
+    if (!ctx || n_reqs < 0 || (n_reqs && !reqs) || !ticket) return PHMM_ERR_ARG;
+    FlatBuilder fbld;
+    phmm_ctx::Inflight f;
+    int64_t p = 0;
+    for (int k = 0; k < n_reqs; ++k) {
+        const phmm_pairs_request &r = reqs[k];
+        if (r.n < 0 || (r.n && (!r.pairs || !r.out))) { ctx->error = "malformed request"; return PHMM_ERR_ARG; }
+        int rc = append_testcases(ctx, fbld, r.pairs, r.n);
+        if (rc != PHMM_OK) return rc;
+        f.scatter.push_back({r.out, p, r.n});
+        p += r.n;
+    }
+    fbld.b.finish();
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return submit_merged(ctx, fbld.b.view, f, ticket);
 }
 
 // ============================================================================================

@@ -56,7 +56,7 @@ class CTestcase(C.Structure):
 
 EXPORTS = ["phmm_abi_version", "phmm_device_count", "phmm_create", "phmm_destroy", "phmm_set_option",
            "phmm_get_option", "phmm_last_error", "phmm_compute_pairs", "phmm_compute_batches",
-           "phmm_compute_flat", "phmm_host_register", "phmm_host_unregister", "phmm_workload_create", "phmm_workload_run", "phmm_workload_results",
+           "phmm_compute_flat", "phmm_submit_pairs", "phmm_submit_flat", "phmm_flatten_pairs", "phmm_wait", "phmm_host_register", "phmm_host_unregister", "phmm_workload_create", "phmm_workload_run", "phmm_workload_results",
            "phmm_workload_destroy", "phmm_partition_lpt", "phmm_batch_costs", "phmm_parse_file", "phmm_parse_buffer",
            "phmm_parsed_batches", "phmm_parsed_free", "phmm_microbench", "phmm_get_tables",
            "phmm_plan_summary", "phmm_cache_write", "phmm_cache_open", "phmm_gatk_init",

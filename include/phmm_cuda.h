@@ -162,6 +162,33 @@ int phmm_compute_pairs(phmm_ctx *ctx, const phmm_testcase *pairs, double *out, i
 int phmm_compute_batches(phmm_ctx *ctx, const phmm_batch *batches, int64_t n_batches);
 int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, double *out, phmm_stats *stats);
 
+/* Asynchronous form of phmm_compute_pairs for a dispatcher that serves several callers: the requests' testcase
+ * arrays (each what one computelikelihoodsboth call receives, IntelPairHmmCSource.cpp:61) are merged into ONE planned
+ * chunk, whose uploads and kernels are queued in a free pipeline slot; the call returns without waiting (the pageable
+ * inputs have been staged by then and may be reused).  phmm_wait(ticket) blocks until that submission -- and every
+ * earlier one -- has finished and copies each request's results into its own `out`.  Up to four submissions are in
+ * flight per context; one thread at a time per context.  libphmm_cuda's own legacy symbols use this to coalesce the
+ * concurrent per-batch calls of the driver's OpenMP threads (PairHMMUnitTest_orig.cpp:271-299). */
+typedef struct {
+    const phmm_testcase *pairs;
+    double *out;
+    int64_t n;
+} phmm_pairs_request;
+int phmm_submit_pairs(phmm_ctx *ctx, const phmm_pairs_request *reqs, int n_reqs, int64_t *ticket);
+int phmm_wait(phmm_ctx *ctx, int64_t ticket);
+/* The same with requests that are flat batches already (what a caller thread gets from phmm_flatten_pairs, doing the
+ * per-pair work of a legacy call itself and in parallel with the other callers): tables are appended, pools copied
+ * back to back.  out receives the request's results in the order of phmm_compute_flat. */
+typedef struct phmm_parsed phmm_parsed;
+typedef struct {
+    const phmm_flat_batches *batches;
+    double *out;
+} phmm_flat_request;
+int phmm_submit_flat(phmm_ctx *ctx, const phmm_flat_request *reqs, int n_reqs, int64_t *ticket);
+/* testcase[] -> flat batches (de-duplicating the strings the pairs share), owned by the returned handle: read with
+ * phmm_parsed_batches, release with phmm_parsed_free.  No device needed. */
+int phmm_flatten_pairs(const phmm_testcase *pairs, int64_t n, phmm_parsed **out, char *err, size_t err_len);
+
 /* Optional: page-lock caller-owned buffers that live across many calls (the pools of phmm_flat_batches, the results
  * array), so that the library's copies run as asynchronous DMA at full PCIe / NVLink-C2C rate instead of being staged
  * through the driver's bounce buffer (cudaHostRegister behind a plain-pointer interface: a cgo / JNI / ctypes caller
@@ -201,7 +228,6 @@ int phmm_batch_costs(const phmm_flat_batches *fb, int fp32_fast, int precision, 
  * Parses what read_testfile / read_batch read (PairHMMUnitTest_orig.cpp:97-213) into flat
  * batches owned by the returned handle; qualities are normalised as the driver does
  * (`normalize`, :88-92: q floor 6, i/d/c floor 0, after subtracting 33). */
-typedef struct phmm_parsed phmm_parsed;
 int phmm_parse_file(const char *path, phmm_parsed **out, char *err, size_t err_len);
 int phmm_parse_buffer(const char *data, size_t len, phmm_parsed **out, char *err, size_t err_len);
 const phmm_flat_batches *phmm_parsed_batches(const phmm_parsed *p);

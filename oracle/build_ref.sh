@@ -79,3 +79,43 @@ if [ -f "$EX/PairHMMUnitTest.cpp" ]; then
     echo "built $OUT/gkl_example_driver_cuda"
   fi
 fi
+
+# ---- the BENCHMARK's own driver, UNMODIFIED (benchmarks/phmm/PairHMMUnitTest_orig.cpp: OpenMP loop over batches,
+# one computelikelihoodsboth call per batch and thread :271-299, "Kernel runtime" line :327), for timing the
+# link-time drop-in.  Its shacc_pairhmm.h pulls in the fork's palisade_header.h -> <palisade.h>, which is not
+# installed; the plaintext driver uses none of it, so a stub header with the few type names palisade_header.h
+# mentions (written here, 20 lines, no PALISADE code) is all it needs.  Linked against the reference objects
+# (libphmm_ref.so carries IntelPairHmmCSource.cpp as is, fork printf included) and against libphmm_cuda.so.
+BP="$REF/benchmarks/phmm"
+if [ -f "$BP/PairHMMUnitTest_orig.cpp" ]; then
+  PS="$OUT/stub_palisade"
+  mkdir -p "$PS/scheme/bfvrns"
+  cat > "$PS/palisade.h" <<'STUB'
+// Stub (oracle/build_ref.sh): type names only, so that the unmodified plaintext driver compiles without PALISADE.
+#pragma once
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+namespace lbcrypto {
+class DCRTPoly {};
+template <class T> class CiphertextImpl {};
+template <class T> using Ciphertext = std::shared_ptr<CiphertextImpl<T>>;
+class PlaintextImpl {};
+using Plaintext = std::shared_ptr<PlaintextImpl>;
+template <class T> class CryptoContextImpl {};
+template <class T> using CryptoContext = std::shared_ptr<CryptoContextImpl<T>>;
+template <class T> struct LPKeyPair {};
+enum SecurityLevel { HEStd_128_classic };
+}
+STUB
+  for f in ciphertext-ser.h cryptocontext-ser.h pubkeylp-ser.h scheme/bfvrns/bfvrns-ser.h; do echo "#pragma once" > "$PS/$f"; done
+  g++ -O2 -std=c++11 -fopenmp -w -I"$PS" -I"$BP" "$BP/PairHMMUnitTest_orig.cpp" -o "$OUT/phmm_orig_driver_ref" \
+      -L"$OUT" -lphmm_ref -Wl,-rpath,'$ORIGIN'
+  echo "built $OUT/phmm_orig_driver_ref"
+  if [ -f "$PKG/libphmm_cuda.so" ]; then
+    g++ -O2 -std=c++11 -fopenmp -w -I"$PS" -I"$BP" "$BP/PairHMMUnitTest_orig.cpp" -o "$OUT/phmm_orig_driver_cuda" \
+        -L"$PKG" -lphmm_cuda -Wl,-rpath,'$ORIGIN/../../genomicsbench_palisade_b200'
+    echo "built $OUT/phmm_orig_driver_cuda"
+  fi
+fi

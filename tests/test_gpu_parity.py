@@ -70,6 +70,110 @@ def test_known_answer_through_the_legacy_symbols():
     assert abs(d.value - (-6.022776589e-01)) < 1e-9
 
 
+def _testcases(fb):
+    rsl, hpl, rso, hpo = fb.pairs()
+    n = len(rsl)
+    tcs = (phmm.CTestcase * max(1, n))()
+    base = {k: getattr(fb, k).ctypes.data for k in ("rs", "q", "i", "d", "c", "hap")}
+    for p in range(n):
+        t = tcs[p]
+        t.rslen, t.haplen = int(rsl[p]), int(hpl[p])
+        ro, ho = int(rso[p]), int(hpo[p])
+        t.rs, t.q, t.i, t.d, t.c = (base["rs"] + ro, base["q"] + ro, base["i"] + ro, base["d"] + ro, base["c"] + ro)
+        t.hap = base["hap"] + ho
+    return tcs, n
+
+
+def test_legacy_symbol_coalesces_concurrent_callers():
+    # the benchmark driver's call pattern (PairHMMUnitTest_orig.cpp:271-299): every OpenMP thread calls
+    # computelikelihoodsboth with one batch at a time; behind the symbol one dispatcher merges whatever calls are
+    # pending into one planned chunk.  Eight threads x several batches each, every result checked against the oracle
+    import threading
+    lib = phmm.load_library()
+    lib["_Z11initPairHMMv"]()
+    fn = lib["_Z22computelikelihoodsbothP8testcasePdi"]
+    fb = synth.generic(123, 48, (2, 40), (1, 9), (20, 260), (30, 500), q_rng=(6, 45), subst=0.05, foreign_frac=0.2)
+    ref = oracle.run_port(fb)
+    bos = fb.batch_out_start
+    subs = [fb.select_batches(np.array([b])) for b in range(fb.n_batches)]
+    packed = [_testcases(s) for s in subs]
+    outs = [np.full(max(1, n), np.nan) for _, n in packed]
+    errs = []
+
+    def worker(tid):
+        try:
+            for b in range(tid, len(subs), 8):
+                tcs, n = packed[b]
+                fn(tcs, outs[b].ctypes.data_as(C.c_void_p), C.c_int(n))
+        except Exception as e:      # pragma: no cover
+            errs.append(e)
+
+    for rep in range(2):
+        th = [threading.Thread(target=worker, args=(k,)) for k in range(8)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+    assert not errs
+    for b, (_, n) in enumerate(packed):
+        want, resc = ref.out[bos[b]:bos[b + 1]], ref.rescued[bos[b]:bos[b + 1]].astype(bool)
+        got = outs[b][:n]
+        assert same_or_close(got[~resc], want[~resc], RTOL_FP32) and same_or_close(got[resc], want[resc], RTOL_FP64), b
+
+
+def test_async_submit_and_wait():
+    # phmm_submit_pairs / phmm_wait: several requests per submission, several submissions in flight, waited for
+    # out of order
+    lib = phmm.load_library()
+
+    class CReq(C.Structure):
+        _fields_ = [("pairs", C.c_void_p), ("out", C.c_void_p), ("n", C.c_int64)]
+
+    fb = synth.generic(321, 14, (2, 30), (1, 8), (20, 250), (30, 400), q_rng=(6, 45), subst=0.05, foreign_frac=0.2)
+    ref = oracle.run_port(fb)
+    bos = fb.batch_out_start
+    packed = [_testcases(fb.select_batches(np.array([b]))) for b in range(fb.n_batches)]
+    outs = [np.full(max(1, n), np.nan) for _, n in packed]
+    eng = phmm.PairHMM()
+    tickets = []
+    for g in range(0, fb.n_batches, 2):          # seven submissions of two requests each: more than the four slots
+        reqs = (CReq * 2)()
+        for k in range(2):
+            tcs, n = packed[g + k]
+            reqs[k] = CReq(C.cast(tcs, C.c_void_p), outs[g + k].ctypes.data, n)
+        t = C.c_int64()
+        eng._check(lib.phmm_submit_pairs(eng._h, reqs, C.c_int(2), C.byref(t)))
+        tickets.append(t.value)
+    assert tickets == sorted(tickets) and len(set(tickets)) == len(tickets)
+    eng._check(lib.phmm_wait(eng._h, C.c_int64(tickets[-1])))
+    eng._check(lib.phmm_wait(eng._h, C.c_int64(tickets[0])))        # already retired: returns at once
+    # the same through phmm_flatten_pairs + phmm_submit_flat (what the legacy symbols' dispatcher does)
+    class CFlatReq(C.Structure):
+        _fields_ = [("batches", C.c_void_p), ("out", C.c_void_p)]
+
+    lib.phmm_parsed_batches.restype = C.c_void_p
+    outs2 = [np.full(max(1, n), np.nan) for _, n in packed]
+    handles = []
+    for tcs, n in packed:
+        h = C.c_void_p()
+        assert lib.phmm_flatten_pairs(tcs, C.c_int64(n), C.byref(h), None, C.c_size_t(0)) == 0
+        handles.append(h)
+    for g in range(0, fb.n_batches, 7):
+        reqs = (CFlatReq * 7)()
+        for k in range(7):
+            reqs[k] = CFlatReq(lib.phmm_parsed_batches(handles[g + k]), outs2[g + k].ctypes.data)
+        t = C.c_int64()
+        eng._check(lib.phmm_submit_flat(eng._h, reqs, C.c_int(7), C.byref(t)))
+    eng._check(lib.phmm_wait(eng._h, t))
+    lib.phmm_parsed_batches.restype = C.POINTER(phmm.CFlatBatches)
+    for h in handles:
+        lib.phmm_parsed_free(h)
+    eng.close()
+    for b, (_, n) in enumerate(packed):
+        assert np.array_equal(outs2[b][:n], outs[b][:n])
+    for b, (_, n) in enumerate(packed):
+        want, resc = ref.out[bos[b]:bos[b + 1]], ref.rescued[bos[b]:bos[b + 1]].astype(bool)
+        assert same_or_close(outs[b][:n][~resc], want[~resc], RTOL_FP32) and same_or_close(outs[b][:n][resc], want[resc], RTOL_FP64)
+
+
 @pytest.mark.parametrize("precision", [phmm.FLOAT_ONLY, phmm.DOUBLE_ONLY])
 def test_single_precision_modes(precision):
     fb, g = load_golden("c1_small")

@@ -246,6 +246,35 @@ def test_batch_costs_and_rescue_prediction():
     assert len(phmm.batch_costs(empty)) == 0
 
 
+def test_flatten_pairs_folds_the_testcase_slab_back_into_batches():
+    # phmm_flatten_pairs: what a caller thread of the legacy symbol does before the dispatcher merges the calls
+    import ctypes as C
+    lib = phmm.load_library()
+    fb = synth.generic(77, 5, (2, 9), (1, 6), (10, 120), (20, 200), q_rng=(6, 45), foreign_frac=0.2)
+    rsl, hpl, rso, hpo = fb.pairs()
+    n = len(rsl)
+    tcs = (phmm.CTestcase * n)()
+    base = {k: getattr(fb, k).ctypes.data for k in ("rs", "q", "i", "d", "c", "hap")}
+    for p in range(n):
+        t = tcs[p]
+        t.rslen, t.haplen = int(rsl[p]), int(hpl[p])
+        t.rs, t.q, t.i, t.d, t.c = (base[k] + int(rso[p]) for k in ("rs", "q", "i", "d", "c"))
+        t.hap = base["hap"] + int(hpo[p])
+    h = C.c_void_p()
+    err = C.create_string_buffer(160)
+    assert lib.phmm_flatten_pairs(tcs, C.c_int64(n), C.byref(h), err, C.c_size_t(160)) == 0
+    got = phmm.flat_from_c(lib.phmm_parsed_batches(h).contents)
+    lib.phmm_parsed_free(h)
+    # the all-pairs slabs fold back into the reads x haplotypes batches they came from, every string stored once
+    assert got.batch_num_reads.tolist() == fb.batch_num_reads.tolist()
+    assert got.batch_num_haps.tolist() == fb.batch_num_haps.tolist()
+    assert len(got.rs) == int(fb.read_len.sum()) and len(got.hap) == int(fb.hap_len.sum())
+    a, b = oracle.run_port(fb), oracle.run_port(got)
+    assert np.array_equal(a.out.view(np.uint64), b.out.view(np.uint64))
+    tcs[3].rslen = 0
+    assert lib.phmm_flatten_pairs(tcs, C.c_int64(n), C.byref(h), err, C.c_size_t(160)) == 2 and b"rslen" in err.value
+
+
 def test_same_shape_parts_of_a_weak_scaling_run():
     a = synth.c2_large(60_000)
     b = synth.same_shape(a, 7)
