@@ -9,12 +9,15 @@
 //                          instead of re-parsing the text when it is at least as new as the input
 // and its final line "PairHMM completed. Kernel runtime: %.2f sec" (:327).  As in the original,
 // parsing is outside the timed region (:243 vs :259).  What differs: all batches are parsed into
-// flat pools (no per-string heap allocation), sharded over the visible B200s longest-first by cell
-// count, and each GPU runs its whole shard as one workload instead of one library call per batch.
+// flat pools (no per-string heap allocation) and the visible B200s pull chunks of consecutive batches, sized by
+// predicted device time, from one shared queue, three chunks in flight per GPU (see main).
 #include <getopt.h>
+#include <malloc.h>
 #include <sys/stat.h>
 #include <sys/time.h>
 
+#include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -25,18 +28,6 @@
 #include "phmm_cuda.h"
 
 namespace {
-
-struct Shard {
-    std::vector<int64_t> batch_ids;
-    std::vector<int32_t> bnr, bnh, read_len, hap_len;
-    std::vector<int64_t> read_off, hap_off;
-    std::vector<int64_t> out_start;      // per batch of the shard: first result index in `out`
-    std::vector<double> out;
-    phmm_flat_batches view;
-    phmm_stats stats;
-    int rc = PHMM_OK;
-    char err[256] = {0};
-};
 
 double now_sec()
 {
@@ -74,6 +65,13 @@ int main(int argc, char **argv)
     }
     if (!path) { usage(argv[0]); return 2; }
     if (loops < 1) loops = 1;
+    // One host thread per GPU plans chunk after chunk: megabytes of task lists allocated and freed every few
+    // milliseconds.  glibc serves such sizes with mmap / munmap, and in ONE process all threads then queue on the
+    // address-space lock and fault every page in again (8 GPUs: 11 % slower per GPU than one GPU alone).  Keep
+    // the memory in the per-thread heaps instead.
+    mallopt(M_MMAP_THRESHOLD, 1 << 30);
+    mallopt(M_TRIM_THRESHOLD, 1 << 30);
+    mallopt(M_TOP_PAD, 64 << 20);
     setbuf(stdout, nullptr);
 
     phmm_parsed *parsed = nullptr;
@@ -106,85 +104,112 @@ int main(int argc, char **argv)
     if (max_gpus > 0 && max_gpus < ngpu) ngpu = max_gpus;
     if (fb->n_batches < ngpu) ngpu = fb->n_batches > 0 ? (int)fb->n_batches : 1;
 
-    // ---- shard batches over GPUs: LPT by exact cell count (Batch::num_cells, :166) -----------
+    // ---- a shared queue of chunks of consecutive batches -------------------------------------------
+    // The reference hands whole batches to OpenMP threads dynamically (schedule(dynamic), :271-276); here the GPUs
+    // pull chunks of consecutive batches from one queue.  A chunk is sized by PREDICTED DEVICE TIME
+    // (phmm_batch_costs: register-tile geometry of every read's kernel class + predicted FP64-rescue work; the
+    // reference's Batch::num_cells, :166, ignores both), about a twelfth of a GPU's share, so that the GPU that
+    // draws the dear batches simply draws fewer chunks.  Chunks are views into the parsed pools (no copy), their
+    // results land at the batch's own place in one output array, and every GPU keeps three chunks in flight
+    // (phmm_submit_flat / phmm_wait), so planning and uploading one chunk hides under the kernels of the others.
     const int64_t nb = fb->n_batches;
-    std::vector<int64_t> cost(nb), rstart(nb + 1, 0), hstart(nb + 1, 0), ostart(nb + 1, 0);
+    std::vector<int64_t> cost(nb > 0 ? nb : 1), rstart(nb + 1, 0), hstart(nb + 1, 0), ostart(nb + 1, 0);
     for (int64_t b = 0; b < nb; ++b) {
         rstart[b + 1] = rstart[b] + fb->batch_num_reads[b];
         hstart[b + 1] = hstart[b] + fb->batch_num_haps[b];
         ostart[b + 1] = ostart[b] + (int64_t)fb->batch_num_reads[b] * fb->batch_num_haps[b];
-        int64_t sr = 0, sh = 0;
-        for (int64_t r = rstart[b]; r < rstart[b + 1]; ++r) sr += fb->read_len[r];
-        for (int64_t h = hstart[b]; h < hstart[b + 1]; ++h) sh += fb->hap_len[h];
-        cost[b] = sr * sh;
     }
-    std::vector<int32_t> owner(nb > 0 ? nb : 1, 0);
-    if (nb > 0 && phmm_partition_lpt(cost.data(), nb, ngpu, owner.data()) != PHMM_OK) return 1;
-
-    std::vector<Shard> shards(ngpu);
-    for (int64_t b = 0; b < nb; ++b) {
-        Shard &s = shards[owner[b]];
-        s.batch_ids.push_back(b);
-        s.bnr.push_back(fb->batch_num_reads[b]);
-        s.bnh.push_back(fb->batch_num_haps[b]);
-        for (int64_t r = rstart[b]; r < rstart[b + 1]; ++r) { s.read_len.push_back(fb->read_len[r]); s.read_off.push_back(fb->read_off[r]); }
-        for (int64_t h = hstart[b]; h < hstart[b + 1]; ++h) { s.hap_len.push_back(fb->hap_len[h]); s.hap_off.push_back(fb->hap_off[h]); }
-        s.out_start.push_back((int64_t)s.out.size());
-        s.out.resize(s.out.size() + (size_t)(ostart[b + 1] - ostart[b]));
+    const char *fast_env = getenv("PHMM_FAST");
+    const int fast = fast_env ? atoi(fast_env) : 0;
+    if (nb > 0 && phmm_batch_costs(fb, fast, 0, cost.data(), nullptr) != PHMM_OK) { fprintf(stderr, "phmm: malformed batches\n"); return 1; }
+    double total_cost = 0;
+    for (int64_t b = 0; b < nb; ++b) total_cost += (double)cost[b];
+    // ~1.2 cost units per cell on typical input: 5e9 .. 5e10 per chunk = 1.5 .. 15 ms of one B200
+    const double chunk_cost = std::min(5e10, std::max(5e9, total_cost / (12.0 * ngpu)));
+    struct Chunk { int64_t b0, b1; };
+    std::vector<Chunk> chunks;
+    {
+        double acc = 0;
+        int64_t b0 = 0;
+        for (int64_t b = 0; b < nb; ++b) {
+            acc += (double)cost[b];
+            if (acc >= chunk_cost || b == nb - 1) { chunks.push_back(Chunk{b0, b + 1}); b0 = b + 1; acc = 0; }
+        }
     }
-    for (Shard &s : shards) {
-        s.view = *fb;
-        s.view.n_batches = (int64_t)s.bnr.size();
-        s.view.batch_num_reads = s.bnr.data();
-        s.view.batch_num_haps = s.bnh.data();
-        s.view.n_reads = (int64_t)s.read_len.size();
-        s.view.read_len = s.read_len.data();
-        s.view.read_off = s.read_off.data();
-        s.view.n_haps = (int64_t)s.hap_len.size();
-        s.view.hap_len = s.hap_len.data();
-        s.view.hap_off = s.hap_off.data();
-    }
+    std::vector<double> out((size_t)std::max<int64_t>(ostart[nb], 1));
 
     // ---- contexts first (table generation + device binding are `initPairHMM`, untimed, :238) ---
     std::vector<phmm_ctx *> ctx(ngpu, nullptr);
     for (int g = 0; g < ngpu; ++g) {
         if (phmm_create(g, &ctx[g]) != PHMM_OK) { fprintf(stderr, "phmm: GPU %d: %s\n", g, phmm_last_error(nullptr)); return 1; }
-        if (const char *f = getenv("PHMM_FAST")) phmm_set_option(ctx[g], PHMM_OPT_FP32_KERNEL, atoi(f));
+        phmm_set_option(ctx[g], PHMM_OPT_FP32_KERNEL, fast);
+        phmm_set_option(ctx[g], PHMM_OPT_FP64_KERNEL, fast);
     }
 
     // ---- timed compute phase (:259-313) ---------------------------------------------------------
+    struct PerGpu { phmm_stats stats; int rc = PHMM_OK; int64_t chunks = 0; double busy_s = 0; char err[256] = {0}; };
+    std::vector<PerGpu> per(ngpu);
+    for (PerGpu &p : per) memset(&p.stats, 0, sizeof p.stats);
     const double t0 = now_sec();
-    std::vector<std::thread> th;
-    for (int g = 0; g < ngpu; ++g)
-        th.emplace_back([&, g]() {
-            Shard &s = shards[g];
-            for (int l = 0; l < loops && s.rc == PHMM_OK; ++l) {
-                s.rc = phmm_compute_flat(ctx[g], &s.view, s.out.empty() ? nullptr : s.out.data(), &s.stats);
-                if (s.rc != PHMM_OK) snprintf(s.err, sizeof s.err, "%s", phmm_last_error(ctx[g]));
-            }
-        });
-    for (auto &t : th) t.join();
+    for (int l = 0; l < loops; ++l) {
+        std::atomic<size_t> next{0};
+        std::vector<std::thread> th;
+        for (int g = 0; g < ngpu; ++g)
+            th.emplace_back([&, g]() {
+                PerGpu &me = per[g];
+                const double tb = now_sec();
+                std::vector<int64_t> tickets;
+                size_t waited = 0;
+                while (me.rc == PHMM_OK) {
+                    const size_t k = next.fetch_add(1);
+                    if (k >= chunks.size()) break;
+                    const Chunk &c = chunks[k];
+                    phmm_flat_batches v = *fb;
+                    v.n_batches = c.b1 - c.b0;
+                    v.batch_num_reads = fb->batch_num_reads + c.b0;
+                    v.batch_num_haps = fb->batch_num_haps + c.b0;
+                    v.n_reads = rstart[c.b1] - rstart[c.b0];
+                    v.read_len = fb->read_len + rstart[c.b0];
+                    v.read_off = fb->read_off + rstart[c.b0];
+                    v.n_haps = hstart[c.b1] - hstart[c.b0];
+                    v.hap_len = fb->hap_len + hstart[c.b0];
+                    v.hap_off = fb->hap_off + hstart[c.b0];
+                    const phmm_flat_request rq{&v, out.data() + ostart[c.b0]};
+                    int64_t t = 0;
+                    me.rc = phmm_submit_flat(ctx[g], &rq, 1, &t);
+                    if (me.rc != PHMM_OK) break;
+                    tickets.push_back(t);
+                    ++me.chunks;
+                    if (tickets.size() - waited >= 3) me.rc = phmm_wait(ctx[g], tickets[waited++], &me.stats);
+                }
+                if (me.rc == PHMM_OK && !tickets.empty()) me.rc = phmm_wait(ctx[g], tickets.back(), &me.stats);
+                if (me.rc != PHMM_OK) snprintf(me.err, sizeof me.err, "%s", phmm_last_error(ctx[g]));
+                me.busy_s += now_sec() - tb;
+            });
+        for (auto &t : th) t.join();
+    }
     const double runtime = now_sec() - t0;
 
     int64_t cells = 0, pairs = 0, rescued = 0;
+    double busy_max = 0, busy_sum = 0;
     for (int g = 0; g < ngpu; ++g) {
-        if (shards[g].rc != PHMM_OK) { fprintf(stderr, "phmm: GPU %d: %s\n", g, shards[g].err); return 1; }
-        cells += shards[g].stats.n_cells;
-        pairs += shards[g].stats.n_pairs;
-        rescued += shards[g].stats.n_rescued;
+        if (per[g].rc != PHMM_OK) { fprintf(stderr, "phmm: GPU %d: %s\n", g, per[g].err); return 1; }
+        cells += per[g].stats.n_cells;
+        pairs += per[g].stats.n_pairs;
+        rescued += per[g].stats.n_rescued;
+        busy_max = std::max(busy_max, per[g].busy_s);
+        busy_sum += per[g].busy_s;
         phmm_destroy(ctx[g]);
     }
+    cells /= loops; pairs /= loops; rescued /= loops;
 
     if (print) {
         // batch order of the input file, r * num_haps + h inside a batch (:316-321)
-        std::vector<int64_t> pos(ngpu, 0);
-        for (int64_t b = 0; b < nb; ++b) {
-            Shard &s = shards[owner[b]];
-            const int64_t k = pos[owner[b]]++;
-            const int64_t n = ostart[b + 1] - ostart[b];
-            for (int64_t j = 0; j < n; ++j) printf("%lf\n", s.out[(size_t)(s.out_start[k] + j)]);
-        }
+        for (int64_t j = 0; j < ostart[nb]; ++j) printf("%lf\n", out[(size_t)j]);
     }
+    fprintf(stderr, "phmm: %zu chunks of consecutive batches pulled from one queue; per GPU:", chunks.size());
+    for (int g = 0; g < ngpu; ++g) fprintf(stderr, " %lld", (long long)per[g].chunks);
+    fprintf(stderr, " (all loops); busiest GPU %.3f s, mean %.3f s\n", busy_max, busy_sum / ngpu);
     fprintf(stderr, "phmm: %lld batches, %lld pairs, %lld cells, %lld FP64-rescued, %d GPU(s), %.1f GCUPS incl. planning and copies; input %s in %.3f s\n",
             (long long)nb, (long long)pairs, (long long)cells, (long long)rescued, ngpu,
             runtime > 0 ? cells * (double)loops / runtime / 1e9 : 0.0, from_cache ? "mapped from cache" : "parsed from text", parse_sec);

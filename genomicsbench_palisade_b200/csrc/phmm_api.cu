@@ -66,9 +66,13 @@ struct Arena {
     uint8_t *base = nullptr;
     size_t cap = 0, off = 0;
     // pinned staging for small chunks (one active region per call): every uploaded piece is laid out in it as
-    // in the arena and goes up with one copy instead of a dozen pageable ones (~8 us of driver time each)
+    // in the arena and goes up with one copy instead of a dozen pageable ones (~8 us of driver time each).  Not
+    // for large chunks: laying 35 MB out in a staging buffer first and copying then is slower than the driver's
+    // own pipelined staging of pageable memory (measured: C2 end to end 0.941 -> 0.935 of resident, the one-GPU
+    // CLI 3009 -> 2729 GCUPS with a 128 MB cap)
     uint8_t *stage = nullptr;
-    static constexpr size_t STAGE_CAP = 4u << 20;
+    size_t stage_cap = 0;
+    static constexpr size_t STAGE_MAX = 4u << 20;
 };
 }  // namespace
 
@@ -106,6 +110,7 @@ struct phmm_ctx {
     };
     std::deque<Inflight> inflight;
     int64_t next_ticket = 0;
+    phmm_stats retired_stats = {};       // of submissions a later submit had to retire itself; handed out by the next phmm_wait
 };
 
 struct ClassDev {
@@ -560,9 +565,15 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     // everything that is uploaded sits in front of d_out: small chunks go up in one copy from pinned staging
     const size_t upload_extent = (size_t)((uint8_t *)w->d_out - base);
     uint8_t *stage = nullptr;
-    if (arena && upload_extent <= Arena::STAGE_CAP) {
-        if (!arena->stage && cudaMallocHost((void **)&arena->stage, Arena::STAGE_CAP) != cudaSuccess) { arena->stage = nullptr; cudaGetLastError(); }
-        stage = arena->stage;
+    if (arena && upload_extent <= Arena::STAGE_MAX) {
+        if (arena->stage_cap < upload_extent) {
+            if (arena->stage) cudaFreeHost(arena->stage);
+            arena->stage = nullptr;
+            const size_t want = std::min<size_t>(Arena::STAGE_MAX, std::max<size_t>(4u << 20, upload_extent + upload_extent / 4));
+            if (cudaMallocHost((void **)&arena->stage, want) == cudaSuccess) arena->stage_cap = want;
+            else { arena->stage = nullptr; arena->stage_cap = 0; cudaGetLastError(); }
+        }
+        if (arena->stage_cap >= upload_extent) stage = arena->stage;
     }
     // dst: device address; staged: the same offset in the staging buffer (the slot is idle: its previous chunk
     // has been retired, so the last copy out of the buffer is complete)
@@ -1229,15 +1240,31 @@ extern "C" int phmm_flatten_pairs(const phmm_testcase *tc, int64_t n, phmm_parse
 // phmm_submit_pairs merges the requests into one set of batches, plans it, queues its uploads and kernels in a
 // free pipeline slot and returns; phmm_wait copies every request's results into its own array.  Up to N_SLOTS
 // submissions are in flight; a submit that finds no free slot retires the oldest first.
-extern "C" int phmm_wait(phmm_ctx *ctx, int64_t ticket)
+extern "C" int phmm_wait(phmm_ctx *ctx, int64_t ticket, phmm_stats *stats)
 {
     if (!ctx) return PHMM_ERR_ARG;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (stats && stats != &ctx->retired_stats && ctx->retired_stats.n_launches) {
+        phmm_stats &a = ctx->retired_stats;
+        stats->n_pairs += a.n_pairs; stats->n_cells += a.n_cells; stats->n_rescued += a.n_rescued; stats->n_guard += a.n_guard;
+        stats->n_tasks += a.n_tasks; stats->h2d_bytes += a.h2d_bytes; stats->d2h_bytes += a.d2h_bytes;
+        stats->n_launches += a.n_launches; stats->n_classes = std::max(stats->n_classes, a.n_classes);
+        stats->ms_fp32 += a.ms_fp32; stats->ms_fp64 += a.ms_fp64; stats->ms_total += a.ms_total;
+        memset(&a, 0, sizeof a);
+    }
     while (!ctx->inflight.empty() && ctx->inflight.front().ticket <= ticket) {
         phmm_ctx::Inflight f = std::move(ctx->inflight.front());
         ctx->inflight.pop_front();
         StreamSet &ss = ctx->ss[f.slot];
-        int rc = wl_finish(ctx, f.w, ss, nullptr);
+        phmm_stats st;
+        int rc = wl_finish(ctx, f.w, ss, &st);
+        if (rc == PHMM_OK && stats) {
+            stats->n_pairs += st.n_pairs; stats->n_cells += st.n_cells; stats->n_rescued += st.n_rescued;
+            stats->n_guard += st.n_guard; stats->n_tasks += st.n_tasks; stats->h2d_bytes += st.h2d_bytes;
+            stats->d2h_bytes += st.n_pairs * (int64_t)sizeof(double); stats->n_launches += st.n_launches;
+            stats->n_classes = std::max(stats->n_classes, st.n_classes);
+            stats->ms_fp32 += st.ms_fp32; stats->ms_fp64 += st.ms_fp64; stats->ms_total += st.ms_total;
+        }
         if (rc == PHMM_OK) {
             for (const phmm_ctx::Inflight::Scatter &sc : f.scatter)
                 if (sc.n > 0 && cudaMemcpyAsync(sc.out, f.w->d_out + sc.p0, (size_t)sc.n * sizeof(double), cudaMemcpyDeviceToHost,
@@ -1257,7 +1284,7 @@ static int submit_merged(phmm_ctx *ctx, const phmm_flat_batches &view, phmm_ctx:
     f.slot = (int)(f.ticket % phmm_ctx::N_SLOTS);
     // the slot's arena and streams must be idle
     for (const phmm_ctx::Inflight &g : ctx->inflight)
-        if (g.slot == f.slot) { int rc = phmm_wait(ctx, g.ticket); if (rc != PHMM_OK) return rc; break; }
+        if (g.slot == f.slot) { int rc = phmm_wait(ctx, g.ticket, &ctx->retired_stats); if (rc != PHMM_OK) return rc; break; }
     PlanOptions popt = plan_options(ctx);
     popt.latency = plan_latency(view, popt);
     StreamSet &ss = ctx->ss[f.slot];

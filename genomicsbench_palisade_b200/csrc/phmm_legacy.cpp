@@ -185,7 +185,7 @@ class Coalescer {
             Flight f = std::move(flights.front());
             flights.pop_front();
             lk.unlock();
-            const int rc = phmm_wait(ctx_, f.ticket);
+            const int rc = phmm_wait(ctx_, f.ticket, nullptr);
             finish(f.reqs, rc);
             lk.lock();
         }

@@ -165,7 +165,7 @@ int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, double *out, p
 /* Asynchronous form of phmm_compute_pairs for a dispatcher that serves several callers: the requests' testcase
  * arrays (each what one computelikelihoodsboth call receives, IntelPairHmmCSource.cpp:61) are merged into ONE planned
  * chunk, whose uploads and kernels are queued in a free pipeline slot; the call returns without waiting (the pageable
- * inputs have been staged by then and may be reused).  phmm_wait(ticket) blocks until that submission -- and every
+ * inputs have been staged by then and may be reused).  phmm_wait(ticket, stats) blocks until that submission -- and every
  * earlier one -- has finished and copies each request's results into its own `out`.  Up to four submissions are in
  * flight per context; one thread at a time per context.  libphmm_cuda's own legacy symbols use this to coalesce the
  * concurrent per-batch calls of the driver's OpenMP threads (PairHMMUnitTest_orig.cpp:271-299). */
@@ -175,7 +175,9 @@ typedef struct {
     int64_t n;
 } phmm_pairs_request;
 int phmm_submit_pairs(phmm_ctx *ctx, const phmm_pairs_request *reqs, int n_reqs, int64_t *ticket);
-int phmm_wait(phmm_ctx *ctx, int64_t ticket);
+/* stats may be NULL; otherwise the counts and kernel times of every submission this call retires (and of those an
+ * earlier phmm_submit_* had to retire to free a slot) are ADDED to it: zero it before the first use. */
+int phmm_wait(phmm_ctx *ctx, int64_t ticket, phmm_stats *stats);
 /* The same with requests that are flat batches already (what a caller thread gets from phmm_flatten_pairs, doing the
  * per-pair work of a legacy call itself and in parallel with the other callers): tables are appended, pools copied
  * back to back.  out receives the request's results in the order of phmm_compute_flat. */

@@ -143,8 +143,10 @@ def test_async_submit_and_wait():
         eng._check(lib.phmm_submit_pairs(eng._h, reqs, C.c_int(2), C.byref(t)))
         tickets.append(t.value)
     assert tickets == sorted(tickets) and len(set(tickets)) == len(tickets)
-    eng._check(lib.phmm_wait(eng._h, C.c_int64(tickets[-1])))
-    eng._check(lib.phmm_wait(eng._h, C.c_int64(tickets[0])))        # already retired: returns at once
+    st = phmm.CStats()
+    eng._check(lib.phmm_wait(eng._h, C.c_int64(tickets[-1]), C.byref(st)))
+    assert st.n_pairs == fb.n_pairs and st.n_cells == fb.n_cells and st.n_rescued == int(ref.rescued.sum())
+    eng._check(lib.phmm_wait(eng._h, C.c_int64(tickets[0]), None))        # already retired: returns at once
     # the same through phmm_flatten_pairs + phmm_submit_flat (what the legacy symbols' dispatcher does)
     class CFlatReq(C.Structure):
         _fields_ = [("batches", C.c_void_p), ("out", C.c_void_p)]
@@ -162,7 +164,7 @@ def test_async_submit_and_wait():
             reqs[k] = CFlatReq(lib.phmm_parsed_batches(handles[g + k]), outs2[g + k].ctypes.data)
         t = C.c_int64()
         eng._check(lib.phmm_submit_flat(eng._h, reqs, C.c_int(7), C.byref(t)))
-    eng._check(lib.phmm_wait(eng._h, t))
+    eng._check(lib.phmm_wait(eng._h, t, None))
     lib.phmm_parsed_batches.restype = C.POINTER(phmm.CFlatBatches)
     for h in handles:
         lib.phmm_parsed_free(h)
