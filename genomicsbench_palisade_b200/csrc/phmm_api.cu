@@ -163,6 +163,7 @@ const int INTS_NTASKS = 64;                       // per FP32 class
 const int INTS_RESC = 128;                        // [MAX_KH_SCALAR + 1]
 const int INTS_GUARD = 128 + 16;
 const int INTS_GUARD64 = 128 + 32;                // fast FP64 kernels: non-finite sums, re-run by the exact FP64 kernel
+const int INTS_RESC_PAIRS = 128 + 48;             // pairs in the rescue lists (a task of the fast kernels holds a run of haplotypes)
 const int INTS_TOTAL = 192;
 
 #define CUDA_TRY(ctx, expr)                                                                   \
@@ -662,7 +663,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     pf.ph2pr = ctx->d_ph2pr_f; pf.mm = ctx->d_mm_f;
     pf.init_const = t.init_f; pf.log10_init = t.log10_init_f;
     pf.out = w->d_out; pf.raw32 = w->d_raw32; pf.raw64 = w->d_raw64; pf.rescued = w->d_rescued;
-    pf.resc = w->d_resc; pf.resc_count = w->d_ints + INTS_RESC;
+    pf.resc = w->d_resc; pf.resc_count = w->d_ints + INTS_RESC; pf.resc_pairs = w->d_ints + INTS_RESC_PAIRS;
     pf.guard = w->d_guard; pf.guard_count = w->d_ints + INTS_GUARD;
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) pf.resc_off[k] = w->resc_off[k];
     pf.mode = mode;
@@ -834,11 +835,12 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
 // After the stream set has drained: list counters and event times of the last launch.
 static int wl_finish(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, phmm_stats *stats)
 {
-    int32_t counts[48];
+    int32_t counts[49];
     CUDA_TRY(ctx, cudaMemcpyAsync(counts, w->d_ints + INTS_RESC, sizeof counts, cudaMemcpyDeviceToHost, ss.main));
     CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
-    int64_t nres = 0, nguard = 0, n64 = 0;
-    for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nres += counts[k]; nguard += counts[16 + k]; n64 += counts[32 + k]; }
+    int64_t nguard = 0, n64 = 0;
+    const int64_t nres = counts[48];
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nguard += counts[16 + k]; n64 += counts[32 + k]; }
     if (n64 > 0) {
         // fast FP64 kernels met non-finite sums (exotic gap-continuation penalties): bit-exact re-run
         int rc = wl_launch(ctx, w, ss, nullptr, counts + 32);

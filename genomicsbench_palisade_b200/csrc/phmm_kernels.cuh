@@ -134,6 +134,51 @@ __host__ __device__ __forceinline__ int rescue_class(int rslen)
 // ------------------------------------------------------------------------------------------
 // Result of one (read, haplotype): policy of computelikelihoodsboth (IntelPairHmmCSource.cpp:69-82).
 // ------------------------------------------------------------------------------------------
+// Decision for one (read, haplotype) FP32 sum: 0 = final (log10 written), 1 = FP64 rescue, 2 = re-decide with the
+// bit-exact FP32 kernel (fast kernels only).
+template <bool FAST>
+__device__ __forceinline__ int classify_result(const KernelParams<float> &P, float res, int64_t oidx, int hap_len, int rslen)
+{
+    P.raw32[oidx] = res;
+    bool redo = false;
+    if (FAST) {
+        const float rel = fmaxf(0.0078125f, (float)(rslen + hap_len) * 2.384e-6f);      // see emit_result
+        redo = !(res <= 3.402823466e+38f) ||
+               (P.mode == 0 && res >= MIN_ACCEPTED_F * (1.0f - rel) && res < MIN_ACCEPTED_F * (1.0f + rel));
+    }
+    if (redo) return 2;
+    if (P.mode == 0 && res < MIN_ACCEPTED_F) return 1;                                    // :73-75
+    P.out[oidx] = (double)__fsub_rn(log10f(res), P.log10_init);                           // :78 (and :97)
+    P.rescued[oidx] = 0;
+    return 0;
+}
+
+// A run of consecutive rescued haplotypes of one read, collected by the last lane of a lane group while it walks a
+// run of haplotypes: the FP64 kernel then fills its wavefront and sets the read up once per run instead of once per
+// pair (C2-shaped input: most rescued pairs belong to reads that fit none of their batch's haplotypes).
+struct RescRun {
+    int64_t stream_off;
+    int32_t ncols, hap0, out0, nh;
+};
+static const int RESC_RUN_HAPS = 4;        // FP64 tasks stay short enough for the queue to balance them
+static const int RESC_RUN_COLS = 2048;
+
+__device__ __forceinline__ void resc_flush(const KernelParams<float> &P, RescRun &pr, int rid, int rslen)
+{
+    Task nt;
+    nt.stream_off = pr.stream_off;
+    nt.ncols = pr.ncols;
+    nt.hap0 = pr.hap0;
+    nt.out0 = pr.out0;
+    nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
+    nt.nh = pr.nh;
+    const int ci = rescue_class(rslen);
+    const int k = atomicAdd(&P.resc_count[ci], 1);
+    P.resc[P.resc_off[ci] + k] = nt;
+    atomicAdd(P.resc_pairs, pr.nh);
+    pr.nh = 0;
+}
+
 template <bool FAST>
 __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float res, int64_t oidx,
                                             int64_t hap_stream_off, int hap_len, int hap_idx,
@@ -168,6 +213,7 @@ __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float 
         } else {
             int k = atomicAdd(&P.resc_count[ci], 1);
             P.resc[P.resc_off[ci] + k] = nt;
+            atomicAdd(P.resc_pairs, 1);
         }
         return;
     }

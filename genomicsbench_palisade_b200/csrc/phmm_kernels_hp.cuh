@@ -50,7 +50,8 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
     constexpr int ECODE = NQ * EQUAD;                  // bytes per code
     constexpr int ETAB = N_CODES * ECODE;
     constexpr int RTAB = (MAX_RUN_HAPS + 2) * 8;       // per run: float iy[], int len[]
-    constexpr int WSM = ETAB + 2 * STREAM_RING + 2 * RTAB;
+    constexpr int WSM = ETAB + 2 * STREAM_RING + 2 * RTAB + 8 * (int)sizeof(RescRun);
+    static_assert(sizeof(RescRun) == 24, "smem_per_warp_hp");
     constexpr uint32_t WMASK = STREAM_RING / 4 - 1;
 
     extern __shared__ __align__(16) uint8_t smem_all[];
@@ -67,6 +68,8 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
     const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(etab) + lane * 16;
     const int gl = lane & (LANES - 1);
     const int grp = lane / LANES;
+    // pending rescue runs of this lane group (touched by its last lane only, at haplotype ends)
+    RescRun *pend = reinterpret_cast<RescRun *>(etab + ETAB + 2 * STREAM_RING + 2 * RTAB) + 2 * grp;
     const bool last_lane = (gl == LANES - 1);
     const int ntasks = *P.ntasks_ptr;
     const uint32_t sh = ((4 - (gl & 3)) & 3) * 8;
@@ -92,6 +95,7 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
             const ReadRec rr = P.reads[rid];
             R = rr.len; roff = rr.off; out_base = rr.out_base;
         }
+        if (last_lane) { pend[0].nh = 0; pend[1].nh = 0; }
         // per-run haplotype tables: column-0 boundary INITIAL_CONSTANT / haplen (:86) and length
         __syncwarp();
 #pragma unroll
@@ -279,8 +283,39 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
                                 const int hl = hltab[h][jh[h]];
                                 if (rid >= 0) {
                                     const float res = h ? sumM.y + sumX.y * fin : sumM.x + sumX.x * fin;   // :342
-                                    emit_result<true>(P, res, out_base + out0[h] + jh[h], stream_off[h] + hapstart[h], hl,
-                                                      hap0[h] + jh[h], out0[h] + jh[h], rid, R);
+                                    const int verdict = classify_result<true>(P, res, out_base + out0[h] + jh[h], hl, R);
+                                    RescRun &pr = pend[h];
+                                    if (verdict == 1) {
+                                        // FP64 rescue: extend the run that ended on the previous haplotype, or start one
+                                        // (reads of the multi-pass FP64 class keep one pair per task: its boundary-row
+                                        // scratch is sized for one haplotype)
+                                        if (pr.nh > 0 && pr.nh < RESC_RUN_HAPS && pr.ncols + hl + SEP_COLS <= RESC_RUN_COLS &&
+                                            rescue_class(R) != 0) {
+                                            pr.nh += 1;
+                                            pr.ncols += hl + SEP_COLS;
+                                        } else {
+                                            if (pr.nh > 0) resc_flush(P, pr, rid, R);
+                                            pr.stream_off = stream_off[h] + hapstart[h];
+                                            pr.ncols = hl + SEP_COLS;
+                                            pr.hap0 = hap0[h] + jh[h];
+                                            pr.out0 = out0[h] + jh[h];
+                                            pr.nh = 1;
+                                        }
+                                    } else {
+                                        if (pr.nh > 0) resc_flush(P, pr, rid, R);
+                                        if (verdict == 2) {      // guard band / non-finite: the bit-exact FP32 kernel decides
+                                            Task nt;
+                                            nt.stream_off = stream_off[h] + hapstart[h];
+                                            nt.ncols = hl + SEP_COLS;
+                                            nt.hap0 = hap0[h] + jh[h];
+                                            nt.out0 = out0[h] + jh[h];
+                                            nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
+                                            nt.nh = 1;
+                                            const int ci = rescue_class(R);
+                                            const int k = atomicAdd(&P.guard_count[ci], 1);
+                                            P.guard[P.resc_off[ci] + k] = nt;
+                                        }
+                                    }
                                 }
                                 hapstart[h] += hl + SEP_COLS;
                             }
@@ -298,6 +333,10 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
             }
         }
         cp_async_wait_all();
+        if (last_lane && rid >= 0) {
+            if (pend[0].nh > 0) resc_flush(P, pend[0], rid, R);
+            if (pend[1].nh > 0) resc_flush(P, pend[1], rid, R);
+        }
     }
 }
 

@@ -99,7 +99,8 @@ static const int MAX_KH_SCALAR = MAX_KH;      // FP64 rescue classes: 32 lanes x
 static inline int smem_per_warp(int kh) { return kh * N_CODES * 256 + STREAM_RING + (MAX_RUN_HAPS + 2) * 12; }
 // haplotype-pair kernels: emission table [N_CODES][kh / 4][32 lanes] of 16 bytes, two stream rings, two
 // run tables (float INITIAL_CONSTANT / haplen + int length)
-static inline int smem_per_warp_hp(int kh) { return ((kh + 3) / 4) * N_CODES * 512 + 2 * STREAM_RING + 2 * (MAX_RUN_HAPS + 2) * 8; }
+// + the pending FP64-rescue run of every (lane group, haplotype run): 8 x 24 bytes
+static inline int smem_per_warp_hp(int kh) { return ((kh + 3) / 4) * N_CODES * 512 + 2 * STREAM_RING + 2 * (MAX_RUN_HAPS + 2) * 8 + 8 * 24; }
 
 template <typename T>
 struct KernelParams {
@@ -120,7 +121,8 @@ struct KernelParams {
     double *raw64;                       // FP64 sums (rescued pairs)
     uint8_t *rescued;
     Task *resc;                          // FP32 kernel: rescue list, FP64 kernel: unused
-    int32_t *resc_count;                 // [MAX_KH_SCALAR + 1] one list per scalar kernel class
+    int32_t *resc_count;                 // [MAX_KH_SCALAR + 1] one list per scalar kernel class (tasks)
+    int32_t *resc_pairs;                 // pairs in those tasks (a task may hold a run of rescued haplotypes)
     int32_t resc_off[MAX_KH_SCALAR + 1]; // start of each class's list inside resc / guard
     int32_t mode;                        // PHMM_OPT_PRECISION
     Task *guard;                         // guard-band list (fast kernel only)
