@@ -460,13 +460,24 @@ class _Solo:
         self.R.torch.cuda.synchronize()
 
 
+def sw_block(R, no_cpu):
+    """tools/sw_bench.py's measurement (device-resident, end to end through sw_align_flat, reference on the host
+    cores with a bit-for-bit comparison of score, offset and CIGAR) as a block of this line."""
+    import types
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import sw_bench
+    from genomicsbench_palisade_b200 import sw
+    a = types.SimpleNamespace(steps=5, warmup=3, pairs=100_000, strategy=sw.SOFTCLIP, no_cpu=no_cpu, no_e2e=False)
+    return sw_bench.measure(a, device=R.local, flush=R.flush_buf, cpu_seconds=4.0)
+
+
 def ncu_traffic():
     """DRAM bytes per step of the FP32 launches (dram__bytes_read.sum + dram__bytes_write.sum) from the newest
     committed ncu --set full capture of this benchmark (C2, one GPU); None when there is none."""
     best = None
     pdir = os.path.join(ROOT, "profiles")
     for f in sorted(os.listdir(pdir)) if os.path.isdir(pdir) else []:
-        if f.endswith("_dram_traffic.json"):
+        if f.endswith("_dram_traffic.json") and "phmm" in json.load(open(os.path.join(pdir, f))):
             best = f
     if not best:
         return None, None
@@ -496,8 +507,9 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.configs is None:
-        args.configs = "c1,c3,c4,c5" if args.workload == "c2" else "none"
-    subs = [c for c in args.configs.split(",") if c and c != "none"]
+        args.configs = "c1,c3,c4,c5,sw" if args.workload == "c2" else "none"
+    subs = [c for c in args.configs.split(",") if c and c not in ("none", "sw")]
+    with_sw = "sw" in args.configs.split(",")
 
     if args.impl == "reference":
         reference_arm(args, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
@@ -586,6 +598,10 @@ def main():
         if rank == 0:
             line["configs"] = blocks
     eng.close()
+    if with_sw and rank == 0:
+        # SURVEY.md 8f row 3 (GKL Smith-Waterman with backtrack, libsw_cuda.so): one GPU, not sharded
+        line["sw"] = sw_block(R, args.no_cpu)
+    R.barrier()
     R.close()
     if rank == 0:
         print(json.dumps(line))

@@ -257,7 +257,7 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
         recs[c].push_back(r);
         max_sum = std::max(max_sum, l1 + l2);
         const int kh = CLASS_KH[c], nw = (kh + 7) / 8;
-        w->class_bt_stride[c] = std::max<int64_t>(w->class_bt_stride[c], (int64_t)(l2 + 31) * nw * 32);
+        w->class_bt_stride[c] = std::max<int64_t>(w->class_bt_stride[c], (int64_t)((l2 + 31 + 7) & ~7) * nw * 32);      // whole tiles of eight steps
         w->class_lr_words[c] = std::max<int32_t>(w->class_lr_words[c], ((l2 + 1) * ((kh + 3) & ~3) + 31) & ~31);
         w->bt_bytes += (int64_t)l2 * ((l1 + kh - 1) / kh) * nw * 4;        // one word per active lane, word slot and step
     }
@@ -464,12 +464,23 @@ extern "C" int sw_align_flat(sw_ctx *ctx, const sw_flat_pairs *fp, const sw_para
         if (fp->ref_len[p] <= 0 || fp->alt_len[p] <= 0) { ctx->error = "sequence of length <= 0"; return SW_ERR_EMPTY_SEQ; }
         total_cells += (int64_t)fp->ref_len[p] * fp->alt_len[p];
     }
-    const int64_t per = std::max<int64_t>(1000000000ll, total_cells / 4 + 1);
+    // chunk sizes as fractions of the work: a small first chunk starts the device early, a small last one leaves
+    // little to copy back after the final kernel; few chunks in between, because every chunk launches every kernel
+    // class again with a fraction of its tasks (SW_CHUNK_SCHED overrides; chunks of at least 1e9 cells)
+    static const std::vector<double> sched = []() {
+        std::vector<double> f;
+        if (const char *e = getenv("SW_CHUNK_SCHED")) {
+            for (const char *q = e; *q;) { char *end; const double v = strtod(q, &end); if (end == q) break; f.push_back(v); q = *end ? end + 1 : end; }
+        }
+        if (f.empty()) f = {0.08, 0.32, 0.40, 0.20};
+        return f;
+    }();
     std::vector<int64_t> cut(1, 0);
     for (int64_t p = 0, acc = 0; p < n; ++p) {
         acc += (int64_t)fp->ref_len[p] * fp->alt_len[p];
-        const int64_t want = cut.size() == 1 ? per / 2 : per;      // a small first chunk starts the device early
-        if (acc >= want || p == n - 1) { cut.push_back(p + 1); acc = 0; }
+        const size_t k = cut.size() - 1;
+        const int64_t want = std::max<int64_t>(1000000000ll, (int64_t)(total_cells * (k < sched.size() ? sched[k] : 1.0)));
+        if ((acc >= want && k + 1 < sched.size()) || p == n - 1) { cut.push_back(p + 1); acc = 0; }
     }
     if (cut.size() == 1) cut.push_back(0);
     const size_t nchunks = cut.size() - 1;

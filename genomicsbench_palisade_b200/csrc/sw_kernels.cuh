@@ -11,8 +11,13 @@
 //     here the diagonal state never leaves registers.
 //   * max(a + b, c) is Blackwell's fused VIADDMNMX (__viaddmax_s32): three of them per cell.
 //   * Backtrack: 4 bits per cell (MATCH/INSERT/DELETE + the two *_EXT flags, :21-25), eight cells of
-//     a lane per 32-bit word, stored at [step][word][lane] -- coalesced 128-byte lines per warp and
-//     step.  The reference writes 16 bits per cell (:170).
+//     a lane per 32-bit word.  The reference writes 16 bits per cell (:170).  Layout in the per-warp
+//     scratch: tiles of eight steps, [tile][lane][step in tile][word], so that the words of one lane
+//     over consecutive steps -- what the traceback walks -- are contiguous (the first layout,
+//     [step][word][lane], made every traceback window touch 32 sectors for 128 useful bytes: DRAM reads as
+//     large as the backtrack writes).  The DP collects a tile in shared memory (the lastrow buffer, idle
+//     until the DP is done) and writes it out with full, coalesced 128-byte stores, lanes holding real
+//     rows only.
 //   * Last column scores go to shared memory.  The last row sits in a register slot that depends on
 //     the pair (row nrow of lane (nrow - 1) / KH): picking it per cell would cost a compare and a
 //     select on the ALU pipe, the pipe that bounds the kernel, so that lane stores all its KH row
@@ -75,8 +80,9 @@ struct Params {
 };
 
 // per-warp shared memory: last row (copied from the L2 scratch after the DP), last column, alt bytes
+static const int BT_TILE = 8;                    // steps per backtrack tile
 struct __align__(16) WarpSmem {
-    int32_t lastrow[MAX_LEN + 1], lastcol[MAX_LEN + 1];
+    int32_t lastrow[MAX_LEN + 1 + 32], lastcol[MAX_LEN + 1];   // lastrow doubles as the tile staging buffer: 32 x (8 NW + 1) words
     uint8_t alt[MAX_LEN + 16];
 };
 
@@ -136,6 +142,13 @@ __device__ __forceinline__ int32_t diag_score(int32_t hd, uint32_t c1, uint32_t 
     return r;
 }
 
+// first backtrack word of (step, lane) in the tiled per-warp scratch
+template <int NW>
+__device__ __forceinline__ int64_t bt_word(int st, int ln)
+{
+    return (((int64_t)(st >> 3) * 32 + ln) * BT_TILE + (st & (BT_TILE - 1))) * NW;
+}
+
 // KH rows per lane; a pair runs in the smallest class with 32 * KH >= len1, so one stripe of the
 // wavefront always covers the whole matrix (MAX_LEN = 32 * 32) and most lanes hold real rows.
 // CUT: keep the MATRIX_MIN_CUTOFF clamp of the diagonal term (parameters large enough for it to bind).
@@ -191,6 +204,9 @@ sw_align_kernel(const Params P)
             int32_t Hbot = 0, Fbot = SW_LOW_INIT;
             const bool lr_store = row_cands && lane == (nrow - 1) / KH;      // last-row candidates: SOFTCLIP / IGNORE only
             const int steps = ncol + lanes_used - 1;
+            constexpr int LSTR = BT_TILE * NW + 1;                           // staging stride per lane (odd: conflict-free)
+            uint32_t *stg = reinterpret_cast<uint32_t *>(S.lastrow);
+            const int tile_words = lanes_used * BT_TILE * NW;                // lanes holding real rows only
             for (int st = 0; st < steps; ++st) {
                 const int j = st - lane + 1;             // this lane's column (1-based)
                 int32_t Ht = __shfl_up_sync(FULL, Hbot, 1);
@@ -221,7 +237,7 @@ sw_align_kernel(const Params P)
                     });
                     Hbot = Ht; Fbot = Ft;
 #pragma unroll
-                    for (int q = 0; q < NW; ++q) bt[((int64_t)st * NW + q) * 32 + lane] = word[q];
+                    for (int q = 0; q < NW; ++q) stg[lane * LSTR + (st & (BT_TILE - 1)) * NW + q] = word[q];
                     if (lr_store) {
                         int4 *dst = reinterpret_cast<int4 *>(lr + (int64_t)j * KH4);
 #pragma unroll
@@ -234,6 +250,22 @@ sw_align_kernel(const Params P)
                         for (int p = 0; p < KH; ++p)
                             if (i0 + p <= nrow) S.lastcol[i0 + p] = Hl[p];
                     }
+                }
+                if ((st & (BT_TILE - 1)) == BT_TILE - 1 || st == steps - 1) {
+                    // tile complete: [lane][step][word] of the lanes in use, contiguous in the scratch
+                    __syncwarp();
+                    uint32_t *dst = bt + (int64_t)(st >> 3) * (32 * BT_TILE * NW) + lane;
+                    if (NW == 3) {
+                        for (int wd = lane; wd < tile_words; wd += 32) dst[wd - lane] = stg[(wd / (BT_TILE * NW)) * LSTR + wd % (BT_TILE * NW)];
+                    } else {
+                        // 32 output words per round = 32 / (8 NW) whole lanes: the staging address is linear in the round
+                        constexpr int LPR = 32 / (BT_TILE * NW);                 // lanes per round: 4, 2, 1
+                        const uint32_t *src = stg + (lane / (BT_TILE * NW)) * LSTR + lane % (BT_TILE * NW);
+#pragma unroll
+                        for (int it = 0; it < 32 / LPR; ++it)
+                            if (it * LPR < lanes_used) dst[it * 32] = src[it * LPR * LSTR];
+                    }
+                    __syncwarp();
                 }
             }
             __syncwarp();
@@ -316,7 +348,7 @@ sw_align_kernel(const Params P)
                     w_st = st;
                     const int s2 = st - lane;
 #pragma unroll
-                    for (int k = 0; k < NW; ++k) wv[k] = (s2 >= 0) ? __ldcg(bt + ((int64_t)s2 * NW + k) * 32 + ln) : 0u;
+                    for (int k = 0; k < NW; ++k) wv[k] = (s2 >= 0) ? __ldcg(bt + bt_word<NW>(s2, ln) + k) : 0u;
                 }
                 w_ln = ln;
                 n_ln = ln - 1;
@@ -324,7 +356,7 @@ sw_align_kernel(const Params P)
                     n_st = min(st - p - 2 + 8, ncol - 1 + n_ln);          // st of (i - p - 1, j - p - 1) in lane ln - 1, + slack
                     const int s2 = n_st - lane;
 #pragma unroll
-                    for (int k = 0; k < NW; ++k) nv[k] = (s2 >= 0) ? __ldcg(bt + ((int64_t)s2 * NW + k) * 32 + n_ln) : 0u;
+                    for (int k = 0; k < NW; ++k) nv[k] = (s2 >= 0) ? __ldcg(bt + bt_word<NW>(s2, n_ln) + k) : 0u;
                 }
             }
             uint32_t mine = wv[0];

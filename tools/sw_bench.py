@@ -35,7 +35,9 @@ def ncu_traffic():
     command at its default size; above the algorithmic bytes because the traceback window re-reads 32 lines per
     refill and partially filled 128-byte lines are written whole."""
     try:
-        return int(json.load(open(os.path.join(ROOT, "profiles", "r1_v9_dram_traffic.json")))["sw"]["traffic_bytes_per_step"])
+        best = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_dram_traffic.json") and
+                      "sw" in json.load(open(os.path.join(ROOT, "profiles", f))))[-1]
+        return int(json.load(open(os.path.join(ROOT, "profiles", best)))["sw"]["traffic_bytes_per_step"])
     except Exception:
         return None
 
@@ -49,13 +51,18 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
+    print(json.dumps(measure(a)))
 
+
+def measure(a, device=0, flush=None, cpu_seconds=10.0):
+    """The whole measurement as a dict (bench.py puts it into its line as the `sw` block)."""
     ps = sw_pairs.synth(20261104 + 30, a.pairs, ref_rng=(100, 600), read_like=0.2)
     cells = ps.n_cells
     import torch
-    torch.cuda.set_device(0)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    eng = sw.SmithWaterman(0)
+    torch.cuda.set_device(device)
+    if flush is None:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    eng = sw.SmithWaterman(device)
     w = eng.workload(ps, stride=64)
     ms, st = [], {}
     for k in range(a.warmup + a.steps):
@@ -109,7 +116,7 @@ def main():
         run = osw.run_ref if kind == "reference" else osw.run_port
         cores = os.cpu_count() or 1
         reps, dt = 0, 0.0
-        while dt < 10.0 and reps < 64:             # about 10 s of CPU work: whole passes over the workload
+        while dt < cpu_seconds and reps < 64:      # about 10 s of CPU work: whole passes over the workload
             t0 = time.perf_counter()
             r = run(ps, PARAMS, a.strategy, nthreads=cores, stride=64)
             dt += time.perf_counter() - t0
@@ -119,8 +126,10 @@ def main():
                                "sample": "%d pass(es) over the whole workload (%.3g cells each, %.1f s in total), one "
                                          "runSWOnePairBT per pair under OpenMP schedule(dynamic,1); GPU results "
                                          "identical: %s" % (reps, cells, dt, ok)}
+        out["parity"] = {"pairs": ps.n_pairs, "identical_score_offset_cigar": bool(ok and np.array_equal(r.score & 0xffff, res.score & 0xffff)),
+                         "against": "reference AVX-512 / AVX2 objects (oracle/_ref/libsw_ref.so)" if kind == "reference" else "C port"}
     eng.close()
-    print(json.dumps(out))
+    return out
 
 
 if __name__ == "__main__":
