@@ -436,7 +436,7 @@ def sub_config(R, eng, name, fast, kind, peak, steps=3, warmup=3):
                     "e2e": {"value": cells / (e2e_ms * 1e-3) / 1e9, "ms_per_step": e2e_ms,
                             "h2d_bytes_per_step": int(R.world * m["h2d"]) if scaling == "replicas" else None,
                             "matches_resident_run": ok_all, "pinned_value": cells / (e2e_pin_ms * 1e-3) / 1e9},
-                    "frac": ach / peak, "rescue_frac": float(m["rescued"].mean()),
+                    "frac": ach / peak, "tile_fill": tile_fill(fb, fast), "rescue_frac": float(m["rescued"].mean()),
                     "rescue_cells_frac": m["resc_cells"] / max(1, fb.n_cells),
                     "imbalance": max(per_rank) / (sum(per_rank) / len(per_rank)),
                     "gpu_launches": int(m["st"]["n_launches"]) * steps,
@@ -458,6 +458,16 @@ class _Solo:
 
     def barrier(self):
         self.R.torch.cuda.synchronize()
+
+
+def tile_fill(fb, fast):
+    """cells / tile cells of rank 0's plan: the share of the FP32 kernels' row steps that are real read rows (a read
+    of R bases occupies kh x lanes rows of its class's register tile; separator columns count as tile cells too)."""
+    from genomicsbench_palisade_b200 import phmm
+    p = phmm.plan_summary(fb, cover=False, fast=fast)
+    return {"real_over_tile": p["cells"] / max(1, p["tile_cells"]),
+            "classes": [{"kh": k[0], "lanes": k[1], "real_over_tile": round(c / max(1, t), 4)}
+                        for k, (c, t) in zip(p["classes"], p["class_cells"])]}
 
 
 def sw_block(R, no_cpu):
@@ -568,7 +578,7 @@ def main():
                          # FP32 lane-operations issued per cell / FFMA lane-ops peak: 6.25 packed instructions per
                          # cell pair in the fast kernels (scaled recurrence, 16-row tiles), 12 unfused in the exact ones
                          "fma_pipe_slot_frac": ach / peak * 2 * ((6.25 if fast else 12.0) / 12.0),
-                         "ms_fp32": m["ms_fp32"], "ms_fp64": m["ms_fp64"]},
+                         "ms_fp32": m["ms_fp32"], "ms_fp64": m["ms_fp64"], "tile_fill": tile_fill(fb, fast)},
             "rescue": {"pairs": int(m["rescued"].sum()), "frac": float(m["rescued"].mean()) if m["rescued"].size else 0.0,
                        "cells": m["resc_cells"], "guard_band_pairs": int(st["n_guard"])},
         }

@@ -1413,7 +1413,7 @@ extern "C" int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s,
 
 // Plan-only summary (no device needed): used by the CPU test-suite to check the host logic.
 extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int seg_cols,
-                                 int64_t *info /* [8 + 4 * 16] */, uint8_t *pair_cover /* [n_pairs] or NULL */)
+                                 int64_t *info /* [8 + 4 * 16 + 2 * 16] */, uint8_t *pair_cover /* [n_pairs] or NULL */)
 {
     if (!fb || !info) return PHMM_ERR_ARG;
     PlanOptions o;
@@ -1435,6 +1435,27 @@ extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int
     }
     for (auto &cp : P.classes) ntasks += (int64_t)cp.ntasks();
     info[6] = ntasks;
+    // info[7] = tile cells over all classes; info[72 + 2c ..] = {cells, tile cells} of class c (c < 16): a read of R
+    // bases occupies kh x lanes rows of its class's register tile (multi-pass classes: whole blocks of rows), so
+    // cells / tile cells is the share of the FP32 work that is not padding
+    int64_t tile_total = 0;
+    for (size_t c = 0; c < P.classes.size(); ++c) {
+        const KClass &kc = P.classes[c].kc;
+        int64_t tile = 0;
+        auto add = [&](int rid, int64_t cols) {
+            if (rid < 0) return;
+            const int rows = kc.kh * kc.lanes;
+            const int64_t blocks = kc.longr ? (P.reads[rid].len + rows) / rows : 1;
+            tile += blocks * rows * cols;
+        };
+        for (auto &t : P.classes[c].htasks)
+            for (int g = 0; g < kc.group(); ++g) add(t.read[g], (int64_t)t.ncols[0] + t.ncols[1]);
+        for (auto &t : P.classes[c].tasks)
+            for (int g = 0; g < kc.group(); ++g) add(t.read[g], t.ncols);
+        tile_total += tile;
+        if (c < 16) { info[72 + 2 * c] = P.classes[c].cells; info[72 + 2 * c + 1] = tile; }
+    }
+    info[7] = tile_total;
     if (pair_cover) {
         // walk every task the way the kernel does and count how often each pair is produced
         for (auto &cp : P.classes)

@@ -298,7 +298,7 @@ def batch_costs(fb: FlatBatches, fast: bool = True, precision: int = BOTH, predi
 def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True, fast=False):
     lib = load_library()
     keep = _Keep(fb)
-    info = np.zeros(8 + 64, np.int64)
+    info = np.zeros(8 + 64 + 32, np.int64)
     cov = np.zeros(max(1, fb.n_pairs), np.uint8) if cover else None
     rc = lib.phmm_plan_summary(C.byref(keep.c), C.c_int(precision | (0x100 if fast else 0)), C.c_int(seg_cols),
                                _ptr(info), _ptr(cov) if cover else None)
@@ -306,8 +306,10 @@ def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True, fast=Fals
         raise PhmmError(rc, "phmm_plan_summary")
     ncls = int(info[2])
     classes = [tuple(int(x) for x in info[8 + 4 * c: 12 + 4 * c]) for c in range(min(ncls, 16))]
+    fill = [(int(info[72 + 2 * c]), int(info[73 + 2 * c])) for c in range(min(ncls, 16))]
     return {"pairs": int(info[0]), "cells": int(info[1]), "n_classes": ncls, "stream_bytes": int(info[3]),
             "max_rslen": int(info[4]), "max_haplen": int(info[5]), "tasks": int(info[6]),
+            "tile_cells": int(info[7]), "class_cells": fill,
             "classes": classes, "cover": cov[:fb.n_pairs] if cover else None}
 
 

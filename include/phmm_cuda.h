@@ -323,7 +323,9 @@ int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s, float *ms)
  * the number of matchToMatchProb entries (8256).  consts_f/d = {INITIAL_CONSTANT, LOG10_INITIAL_CONSTANT}.
  * phmm_plan_summary: runs the planner only (precision | 0x100 = plan as PHMM_OPT_FP32_KERNEL 1 does:
  * haplotype-pair tasks, two runs of haplotypes per read).  info[0..6] = pairs, cells, classes, stream bytes,
- * max rslen, max haplen, tasks; info[8 + 4c ..] = {kh, lanes, vl, tasks} of class c (c < 16);
+ * max rslen, max haplen, tasks, tile cells (what the FP32 kernels compute: kh x lanes rows per read, separator
+ * columns included); info[8 + 4c ..] = {kh, lanes, vl, tasks} and info[72 + 2c ..] = {cells, tile cells} of class c
+ * (c < 16; info holds 104 values);
  * pair_cover[p] is incremented once for every task that produces pair p. */
 int phmm_get_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d, float *consts_f,
                     double *consts_d);

@@ -244,6 +244,12 @@ def test_batch_costs_and_rescue_prediction():
     assert load.max() / load.mean() < 1.05
     empty = synth.generic(1, 0, (1, 2), (1, 2), (10, 20), (10, 20))
     assert len(phmm.batch_costs(empty)) == 0
+    # the planner's own account of padding: cells against the register-tile cells the FP32 kernels compute
+    for fast in (False, True):
+        p = phmm.plan_summary(fb, fast=fast, cover=False)
+        assert sum(c for c, _ in p["class_cells"]) == p["cells"] == fb.n_cells
+        assert sum(t for _, t in p["class_cells"]) == p["tile_cells"] and all(t >= c for c, t in p["class_cells"])
+        assert 0.85 < p["cells"] / p["tile_cells"] < 1.0
 
 
 def test_flatten_pairs_folds_the_testcase_slab_back_into_batches():
