@@ -134,6 +134,9 @@ struct phmm_workload {
     uint8_t *d_pool = nullptr;        // 5 read pools back to back
     int64_t pool_stride = 0;
     uint8_t *d_stream = nullptr;
+    uint8_t *d_hapraw = nullptr;      // referenced pieces of the caller's haplotype pool (raw bases)
+    HapSrc *d_hapsrc = nullptr;
+    uint8_t *d_unused = nullptr;      // placeholder of whichever of the two haplotype-stream pieces is not in use
     int32_t *d_hap_len = nullptr;
     ReadRec *d_reads = nullptr;
     Task *d_tasks = nullptr;
@@ -183,6 +186,20 @@ double wall_ms()
 }
 
 }  // namespace
+
+// Builds the haplotype stream on the device: one warp per haplotype turns its raw bases into code bytes at its
+// columns (base_code(): ConvertChar + the match rule of precompute_masks_, phmm_types.h); separator and slack
+// bytes stay at the 0 the stream was set to.
+__global__ void phmm_code_stream_kernel(const uint8_t *__restrict__ raw, const phmm::HapSrc *__restrict__ tab, int n,
+                                        uint8_t *__restrict__ stream)
+{
+    const int warp = (int)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (warp >= n) return;
+    const phmm::HapSrc hs = tab[warp];
+    const uint8_t *src = raw + hs.src;
+    uint8_t *dst = stream + hs.dst;
+    for (int k = lane; k < hs.len; k += 32) dst[k] = phmm::base_code(src[k]);
+}
 
 namespace phmm {
 KernelF32 lookup_f32(const KClass &kc, bool fast)
@@ -502,15 +519,19 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     // ---- one allocation, carved into 256-byte aligned pieces ------------------------------------
     const size_t np = (size_t)std::max<int64_t>(1, P.n_pairs);
     struct Piece { void **ptr; size_t bytes; const char *name; };
+    const bool host_coded = !P.stream.empty();       // small call: the stream is uploaded, not built on the device
     const Piece pieces[] = {
         {(void **)&w->d_pool, (size_t)(5 * w->pool_stride), "read pools"},
-        {(void **)&w->d_stream, P.stream.size(), "haplotype stream"},
+        {(void **)&w->d_hapraw, (size_t)P.hap_pool_len, "haplotype bases"},
+        {(void **)&w->d_hapsrc, P.hap_src.size() * sizeof(HapSrc), "haplotype table"},
+        {(void **)(host_coded ? &w->d_stream : &w->d_unused), host_coded ? (size_t)P.stream_len : 0, "haplotype stream (uploaded)"},
         {(void **)&w->d_hap_len, P.hap_len.size() * sizeof(int32_t), "hap_len"},
         {(void **)&w->d_reads, P.reads.size() * sizeof(ReadRec), "reads"},
         {(void **)&w->d_tasks, (size_t)ntasks * sizeof(Task), "tasks"},
         {(void **)&w->d_htasks, (size_t)nhtasks * sizeof(HTask), "htasks"},
         {(void **)&w->d_ints, INTS_TOTAL * sizeof(int32_t), "ints"},
         {(void **)&w->d_out, np * sizeof(double), "out"},
+        {(void **)(host_coded ? &w->d_unused : &w->d_stream), host_coded ? 0 : (size_t)P.stream_len, "haplotype stream"},
         {(void **)&w->d_raw64, np * sizeof(double), "raw64"},
         {(void **)&w->d_raw32, np * sizeof(float), "raw32"},
         {(void **)&w->d_rescued, np, "rescued"},
@@ -588,10 +609,15 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
             WL_TRY(put(w->d_pool + k * w->pool_stride + sg.dst, pools[k] + sg.src, (size_t)sg.len));
             h2d += sg.len;
         }
-    WL_TRY(put(w->d_stream, P.stream.data(), P.stream.size()));
+    for (const Plan::Segment &sg : P.hap_segments) {
+        WL_TRY(put(w->d_hapraw + sg.dst, fb->hap + sg.src, (size_t)sg.len));
+        h2d += sg.len;
+    }
+    WL_TRY(put(w->d_hapsrc, P.hap_src.data(), P.hap_src.size() * sizeof(HapSrc)));
+    if (host_coded) { WL_TRY(put(w->d_stream, P.stream.data(), P.stream.size())); h2d += (int64_t)P.stream.size(); }
     WL_TRY(put(w->d_hap_len, P.hap_len.data(), P.hap_len.size() * sizeof(int32_t)));
     WL_TRY(put(w->d_reads, P.reads.data(), P.reads.size() * sizeof(ReadRec)));
-    h2d += (int64_t)P.stream.size() + (int64_t)P.hap_len.size() * 4 + (int64_t)P.reads.size() * sizeof(ReadRec);
+    h2d += (int64_t)P.hap_src.size() * sizeof(HapSrc) + (int64_t)P.hap_len.size() * 4 + (int64_t)P.reads.size() * sizeof(ReadRec);
     for (size_t c = 0; c < P.classes.size(); ++c) {
         WL_TRY(put(w->d_tasks + w->classes[c].task_off, P.classes[c].tasks.data(), P.classes[c].tasks.size() * sizeof(Task)));
         WL_TRY(put(w->d_htasks + w->classes[c].task_off, P.classes[c].htasks.data(), P.classes[c].htasks.size() * sizeof(HTask)));
@@ -601,6 +627,13 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     // vectors and `ints` may be released right after)
     WL_TRY(put(w->d_ints, ints, sizeof ints));
     if (stage) WL_TRY(cudaMemcpyAsync(base, stage, upload_extent, cudaMemcpyHostToDevice, up));
+    // the haplotype stream: zero (separator columns, alignment gaps, slack), then the code bytes from the raw bases
+    if (!host_coded) WL_TRY(cudaMemsetAsync(w->d_stream, 0, (size_t)P.stream_len, up));
+    if (!host_coded && !P.hap_src.empty()) {
+        const int nh = (int)P.hap_src.size();
+        phmm_code_stream_kernel<<<(nh + 7) / 8, 256, 0, up>>>(w->d_hapraw, w->d_hapsrc, nh, w->d_stream);
+        WL_TRY(cudaGetLastError());
+    }
     WL_TRY(cudaMemsetAsync(w->d_raw64, 0, np * sizeof(double), up));
     WL_TRY(cudaMemsetAsync(w->d_rescued, 0, np, up));
     // after the uploads (the staged copy covers the upload pieces' zones), before any kernel of this workload
@@ -610,6 +643,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
 #undef WL_TRY
     w->h2d_bytes = h2d;
     // host copies of the bulky plan parts are no longer needed
+    std::vector<HapSrc>().swap(P.hap_src);
     std::vector<uint8_t>().swap(P.stream);
     for (auto &cp : P.classes) { std::vector<Task>().swap(cp.tasks); std::vector<HTask>().swap(cp.htasks); }
     *out = w;
@@ -1425,7 +1459,7 @@ extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int
     int rc = build_plan(*fb, o, &P, &err);
     if (rc != PHMM_OK) return rc;
     info[0] = P.n_pairs; info[1] = P.n_cells; info[2] = (int64_t)P.classes.size();
-    info[3] = (int64_t)P.stream.size(); info[4] = P.max_rslen; info[5] = P.max_haplen;
+    info[3] = P.stream_len; info[4] = P.max_rslen; info[5] = P.max_haplen;
     int64_t ntasks = 0;
     for (size_t c = 0; c < P.classes.size() && c < 16; ++c) {
         info[8 + 4 * c + 0] = P.classes[c].kc.kh;

@@ -44,16 +44,24 @@ struct ClassPlan {
     int64_t pairs = 0;
 };
 
+static const int64_t HOST_CODED_STREAM_MAX = 96 << 10;
+
 struct Plan {
+    // Referenced pieces of a caller's byte pool, packed back to back on the device: bytes [src, src + len) go to
+    // device pool offset dst.
+    struct Segment { int64_t src, len, dst; };
     std::vector<ReadRec> reads;
-    std::vector<uint8_t> stream;         // coded haplotype columns (+ STREAM_SLACK)
+    int64_t stream_len = 0;              // bytes of the coded haplotype stream (+ STREAM_SLACK), built on the device ...
+    std::vector<uint8_t> stream;         // ... unless the call is small: then coded here (stream_len <= HOST_CODED_STREAM_MAX)
+    std::vector<HapSrc> hap_src;         // per haplotype: raw bases -> stream columns
+    std::vector<Segment> hap_segments;   // referenced pieces of the caller's haplotype pool (declared below)
+    int64_t hap_pool_len = 0;
     std::vector<int32_t> hap_len;        // stream order, + 1 slack entry
     std::vector<ClassPlan> classes;
     int64_t n_pairs = 0, n_cells = 0;
     int latency = 0;                     // planned for the latency of a small call (PlanOptions::latency)
     // Referenced pieces of the caller's read pools, packed back to back on the device: bytes
     // [src, src + len) of each of the five pools go to device pool offset dst.
-    struct Segment { int64_t src, len, dst; };
     std::vector<Segment> segments;
     int64_t pool_len = 0;                // sum of segment lengths
     int64_t resc_cap[MAX_KH_SCALAR + 1]; // pairs whose read falls in each scalar class

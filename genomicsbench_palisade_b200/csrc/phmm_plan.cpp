@@ -159,20 +159,54 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
             }
         }
         hap_col[fb.n_haps] = total;
-        P.stream.assign((size_t)total + STREAM_SLACK, 0);
+        // The code bytes themselves are produced on the device (phmm_code_stream_kernel, phmm_api.cu): the host only
+        // says where every haplotype's raw bases go.  (Coding them here, byte-wise, was 40 % of the planning time of
+        // small-batch input, and planning is what bounds the end-to-end rate there.)
+        P.stream_len = total + STREAM_SLACK;
         P.hap_len.assign((size_t)fb.n_haps + 1, 1);
-        for (h = 0; h < fb.n_haps; ++h) {
-            const uint8_t *__restrict src = fb.hap + fb.hap_off[h];
-            uint8_t *__restrict dst = P.stream.data() + hap_col[h];
-            const int len = fb.hap_len[h];
-            // base_code() without a table or a branch, so that the compiler turns it into byte-wide SIMD
-            // compares (a 256-entry lookup runs at ~1 byte/ns and was half of the planning time)
-            for (int k = 0; k < len; ++k) {
-                const uint8_t b = src[k];
-                dst[k] = (uint8_t)(CODE_A + (CODE_C - CODE_A) * (b == 'C') + (CODE_T - CODE_A) * (b == 'T') +
-                                   (CODE_G - CODE_A) * (b == 'G') + (CODE_N - CODE_A) * (b == 'N'));
+        if (P.stream_len <= HOST_CODED_STREAM_MAX) {
+            // a small call (an active region or a few): coding a few kilobytes here is cheaper than a memset and a
+            // kernel launch, and the stream then goes up with everything else in the one staged copy
+            P.stream.assign((size_t)P.stream_len, 0);
+            for (h = 0; h < fb.n_haps; ++h) {
+                const uint8_t *src = fb.hap + fb.hap_off[h];
+                uint8_t *dstb = P.stream.data() + hap_col[h];
+                for (int k = 0; k < fb.hap_len[h]; ++k) dstb[k] = base_code(src[k]);
+                P.hap_len[h] = fb.hap_len[h];
             }
-            P.hap_len[h] = len;
+        } else {
+        P.hap_src.resize((size_t)fb.n_haps);
+        bool hsorted = true;
+        for (h = 0; h < fb.n_haps; ++h) {
+            P.hap_len[h] = fb.hap_len[h];
+            if (h && fb.hap_off[h] < fb.hap_off[h - 1]) hsorted = false;
+        }
+        // referenced pieces of the caller's haplotype pool, packed as the read pools are
+        std::vector<int64_t> horder;
+        if (!hsorted) {
+            horder.resize((size_t)fb.n_haps);
+            for (h = 0; h < fb.n_haps; ++h) horder[h] = h;
+            std::sort(horder.begin(), horder.end(), [&](int64_t x, int64_t y) { return fb.hap_off[x] < fb.hap_off[y]; });
+        }
+        std::vector<int64_t> seg_of_hap((size_t)fb.n_haps);
+        int64_t dst = 0;
+        for (int64_t k = 0; k < fb.n_haps; ++k) {
+            const int64_t hh = hsorted ? k : horder[k];
+            const int64_t off = fb.hap_off[hh], end = off + fb.hap_len[hh];
+            if (P.hap_segments.empty() || off > P.hap_segments.back().src + P.hap_segments.back().len + 64) {
+                if (!P.hap_segments.empty()) dst += (P.hap_segments.back().len + 15) & ~(int64_t)15;
+                P.hap_segments.push_back(Plan::Segment{off, 0, dst});
+            }
+            Plan::Segment &sg = P.hap_segments.back();
+            sg.len = std::max(sg.len, end - sg.src);
+            seg_of_hap[hh] = (int64_t)P.hap_segments.size() - 1;
+        }
+        if (!P.hap_segments.empty()) dst += P.hap_segments.back().len;
+        P.hap_pool_len = dst;
+        for (h = 0; h < fb.n_haps; ++h) {
+            const Plan::Segment &sg = P.hap_segments[seg_of_hap[h]];
+            P.hap_src[h] = HapSrc{fb.hap_off[h] - sg.src + sg.dst, hap_col[h], fb.hap_len[h], 0};
+        }
         }
     }
 
@@ -212,7 +246,19 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
     // instead of leaving part of a warp idle.
     struct BatchInfo { int64_t r0, h0, out0, cols; };
     std::vector<BatchInfo> binfo((size_t)fb.n_batches);
-    std::vector<std::vector<int32_t>> rl((size_t)fb.n_batches * ncls);
+    // flat storage: the lists of batch b, class c are rl_idx[rl_off[b * ncls + c] .. rl_off[b * ncls + c + 1])
+    // (one vector per batch and class made thousands of small allocations on 'small'-shaped input)
+    std::vector<int32_t> rl_idx;
+    std::vector<int64_t> rl_off((size_t)fb.n_batches * ncls + 1, 0);
+    rl_idx.reserve((size_t)fb.n_reads);
+    std::vector<std::vector<int32_t>> scratch(ncls);     // the lists of the batch at hand; capacity is kept
+    struct ListView {
+        const int32_t *p; size_t n;
+        size_t size() const { return n; }
+        bool empty() const { return n == 0; }
+        int32_t operator[](size_t k) const { return p[k]; }
+    };
+    auto rl = [&](size_t k) { return ListView{rl_idx.data() + rl_off[k], (size_t)(rl_off[k + 1] - rl_off[k])}; };
     std::vector<int> order(ncls);
     for (size_t c = 0; c < ncls; ++c) order[c] = (int)c;
     std::sort(order.begin(), order.end(), [&](int x, int y) {
@@ -227,7 +273,8 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
             int64_t sum_h = 0;
             for (int k = 0; k < bnh; ++k) sum_h += fb.hap_len[h0 + k];
             binfo[b] = BatchInfo{r0, h0, out0, sum_h + (int64_t)bnh * SEP_COLS};
-            std::vector<int32_t> *by_class = &rl[(size_t)b * ncls];
+            for (auto &v : scratch) v.clear();
+            std::vector<int32_t> *by_class = scratch.data();
             for (int k = 0; k < bnr; ++k) {
                 const int64_t r = r0 + k;
                 ReadRec &rr = P.reads[r];
@@ -256,6 +303,10 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
                         P.classes[c].cells += (int64_t)P.reads[r].len * sum_h;
                         P.classes[c].pairs += bnh;
                     }
+            for (size_t c = 0; c < ncls; ++c) {
+                rl_idx.insert(rl_idx.end(), by_class[c].begin(), by_class[c].end());
+                rl_off[(size_t)b * ncls + c + 1] = (int64_t)rl_idx.size();
+            }
             P.n_pairs += (int64_t)bnr * bnh;
             out0 += (int64_t)bnr * bnh;
             r0 += bnr;
@@ -280,7 +331,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
         for (int64_t b = 0; b < fb.n_batches; ++b)
             for (size_t c = 0; c < ncls; ++c) {
                 const KClass &kc = P.classes[c].kc;
-                const int64_t nr = (int64_t)rl[(size_t)b * ncls + c].size();
+                const int64_t nr = (int64_t)rl((size_t)b * ncls + c).size();
                 if (!nr) continue;
                 const int runs = runs_of(b, cols, kc.hp != 0);
                 n += (kc.hp ? (runs + 1) / 2 : runs) * ((nr + kc.group() - 1) / kc.group());
@@ -309,7 +360,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
             if (bnh == 0) continue;
             bool used = false;
             for (size_t c = 0; c < ncls && !used; ++c)
-                used = (P.classes[c].kc.hp ? 1 : 0) == kind && !rl[(size_t)b * ncls + c].empty();
+                used = (P.classes[c].kc.hp ? 1 : 0) == kind && !rl((size_t)b * ncls + c).empty();
             if (!used) continue;
             const int64_t h0 = binfo[b].h0, total = binfo[b].cols;
             int n = runs_of(b, seg_cols, kind == 1);
@@ -353,7 +404,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
                 for (size_t c = 0; c < ncls; ++c) {
                     const KClass &kc = P.classes[c].kc;
                     if ((kc.hp ? 1 : 0) != kind) continue;
-                    const size_t nr = rl[(size_t)b * ncls + c].size();
+                    const size_t nr = rl((size_t)b * ncls + c).size();
                     n_of[c] += (nr + kc.group() - 1) / kc.group();
                 }
             }
@@ -372,7 +423,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
             for (size_t c = 0; c < ncls; ++c) {
                 const KClass &kc = P.classes[c].kc;
                 if (kc.hp) continue;
-                const std::vector<int32_t> &v = rl[(size_t)rn.b * ncls + c];
+                const ListView v = rl((size_t)rn.b * ncls + c);
                 const int g = kc.group();
                 for (size_t i = 0; i < v.size(); i += g) {
                     Task t;
@@ -400,7 +451,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
             for (size_t c = 0; c < ncls; ++c) {
                 const KClass &kc = P.classes[c].kc;
                 if (!kc.hp) continue;
-                const std::vector<int32_t> &v = rl[(size_t)rn[0].b * ncls + c];
+                const ListView v = rl((size_t)rn[0].b * ncls + c);
                 const int g = kc.group();
                 for (size_t i = 0; i < v.size(); i += g) {
                     HTask t;

@@ -14,6 +14,9 @@ namespace phmm {
 static const uint8_t CODE_SEP = 0, CODE_A = 1, CODE_C = 2, CODE_T = 3, CODE_G = 4, CODE_N = 5;
 static const int N_CODES = 6;
 
+#ifdef __CUDACC__
+__host__ __device__
+#endif
 static inline uint8_t base_code(uint8_t b)
 {
     switch (b) {
@@ -31,6 +34,15 @@ struct ReadRec {
     int64_t out_base;    // result index of (this read, haplotype 0 of its batch)
     int32_t len;
     int32_t batch;
+};
+
+// Where the raw bases of one haplotype sit in the uploaded haplotype pool and where its code bytes go in the
+// haplotype stream (phmm_code_stream_kernel).
+struct HapSrc {
+    int64_t src;         // offset into the device copy of the referenced haplotype-pool pieces
+    int64_t dst;         // first column in the haplotype stream
+    int32_t len;
+    int32_t pad_;
 };
 
 // One unit of work for one warp: up to MAX_GROUP reads streamed against the same run of
