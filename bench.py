@@ -56,6 +56,9 @@ WORKLOADS = {
     "c5": (lambda: synth.c5_skewed(10_000_000), "strong",
            "C5 length-skewed sweep: ONE 10 M-pair set (reads 100/150/250 bp, haplotypes log-uniform 100-5000 bp) "
            "sharded over the GPUs by the length-balanced scheduler"),
+    "skew": (lambda: synth.skewed_rescue(4_000_000), "strong",
+             "scheduler test: C2-shaped, 4 M pairs, every third batch 60 % unrelated reads (rescued in FP64): equal "
+             "cells are not equal time"),
     "tiny": (lambda: synth.generic(synth.SEED0 + 50, 12, (5, 30), (2, 10), (100, 250), (150, 473), foreign_frac=0.05,
                                    name="tiny"), "weak", "tiny"),
 }

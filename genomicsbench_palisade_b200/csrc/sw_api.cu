@@ -65,8 +65,8 @@ struct Slot {
 struct sw_ctx {
     int device = 0, sm_count = 0;
     // slot 0 also serves the device-resident workload API; sw_align_flat pipelines chunks of pairs
-    // through both (upload of one chunk under the kernels of the other)
-    static const int N_SLOTS = 2;
+    // through all three (planning + upload of one chunk under the kernels of the others)
+    static const int N_SLOTS = 3;
     Slot slot[N_SLOTS];
     int blocks_per_sm[N_CLASSES] = {0};
     std::string error;
@@ -265,13 +265,19 @@ static int wl_create(sw_ctx *ctx, const sw_flat_pairs *fp, int32_t cigar_stride,
     std::vector<PairRec> all;
     all.reserve((size_t)n);
     int64_t bt_words = 0, warps_sum = 0;
+    std::vector<int32_t> bucket_at(4098);
     for (int c = 0; c < N_CLASSES; ++c) {
-        std::stable_sort(recs[c].begin(), recs[c].end(), [](const PairRec &a, const PairRec &b) {
-            return (int64_t)a.ref_len * a.alt_len > (int64_t)b.ref_len * b.alt_len;
-        });
+        // longest first, by a counting sort over cells / 256 (len <= 1024 each: 4097 buckets): the queue only needs
+        // the long tasks early, and a comparison sort of 1e5 32-byte records cost as much as a tenth of the kernels
         w->class_off[c] = (int64_t)all.size();
         w->class_ntasks[c] = (int32_t)recs[c].size();
-        all.insert(all.end(), recs[c].begin(), recs[c].end());
+        std::fill(bucket_at.begin(), bucket_at.end(), 0);
+        auto key = [](const PairRec &r) { return 4096 - (int)(((int64_t)r.ref_len * r.alt_len) >> 8); };   // 0 = longest
+        for (const PairRec &r : recs[c]) ++bucket_at[(size_t)key(r) + 1];
+        for (size_t k = 1; k < bucket_at.size(); ++k) bucket_at[k] += bucket_at[k - 1];
+        const size_t base_at = all.size();
+        all.resize(base_at + recs[c].size());
+        for (const PairRec &r : recs[c]) all[base_at + (size_t)bucket_at[(size_t)key(r)]++] = r;
         const int64_t full = (int64_t)ctx->blocks_per_sm[c] * ctx->sm_count;
         const int64_t want = ((int64_t)recs[c].size() + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
         w->class_grid[c] = (int)std::max<int64_t>(1, std::min(full, want));
@@ -484,8 +490,8 @@ extern "C" int sw_align_flat(sw_ctx *ctx, const sw_flat_pairs *fp, const sw_para
     }
     if (cut.size() == 1) cut.push_back(0);
     const size_t nchunks = cut.size() - 1;
-    sw_workload *wl[sw_ctx::N_SLOTS] = {nullptr, nullptr};
-    size_t chunk_of[sw_ctx::N_SLOTS] = {0, 0};
+    sw_workload *wl[sw_ctx::N_SLOTS] = {};
+    size_t chunk_of[sw_ctx::N_SLOTS] = {};
     sw_stats agg;
     memset(&agg, 0, sizeof agg);
     auto retire = [&](int slot) -> int {

@@ -227,6 +227,24 @@ def c5_skewed(n_pairs=10_000_000, seed=SEED0 + 5):
                      foreign_subst=0.25)
 
 
+def skewed_rescue(min_pairs=2_000_000, seed=SEED0 + 6, dirty_every=3, dirty_frac=0.6):
+    """C2-shaped batches of which every `dirty_every`-th holds mostly reads that fit none of its haplotypes (a
+    contaminated or mis-assembled region): their pairs are computed twice, the second time in FP64, so equal
+    cells are far from equal device time.  The scheduler test case for balancing by predicted time."""
+    base = c2_large(min_pairs, seed=seed)
+    rng = np.random.Generator(np.random.PCG64(seed + 1))
+    brs = base.batch_read_start
+    rs = base.rs.copy()
+    for b in range(0, base.n_batches, dirty_every):
+        for r in range(brs[b], brs[b + 1]):
+            if rng.random() < dirty_frac:
+                o, n = int(base.read_off[r]), int(base.read_len[r])
+                sub = rng.random(n) < 0.25
+                rs[o:o + n] = np.where(sub, ACGT[rng.integers(0, 4, n)], rs[o:o + n])
+    return FlatBatches(base.batch_num_reads, base.batch_num_haps, base.read_len, base.read_off, rs, base.q, base.i,
+                       base.d, base.c, base.hap_len, base.hap_off, base.hap, dict(base.meta, workload="skewed-rescue"))
+
+
 def edge_cases(seed=SEED0 + 9, max_read_len=None):
     """Small adversarial batches: R > H, length-1 reads and haplotypes, N bases on both sides,
     bytes outside ACGTN (the reference maps them to 'A', `pairhmm_common.h:27,34-38`), reads
