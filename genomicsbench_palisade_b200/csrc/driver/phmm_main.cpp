@@ -125,7 +125,9 @@ int main(int argc, char **argv)
     double total_cost = 0;
     for (int64_t b = 0; b < nb; ++b) total_cost += (double)cost[b];
     // ~1.2 cost units per cell on typical input: 5e9 .. 5e10 per chunk = 1.5 .. 15 ms of one B200
-    const double chunk_cost = std::min(5e10, std::max(5e9, total_cost / (12.0 * ngpu)));
+    // (PHMM_CLI_CHUNK_COST overrides: tests use it to cut small inputs into many chunks)
+    const double chunk_cost = getenv("PHMM_CLI_CHUNK_COST") ? atof(getenv("PHMM_CLI_CHUNK_COST"))
+                                                            : std::min(5e10, std::max(5e9, total_cost / (12.0 * ngpu)));
     struct Chunk { int64_t b0, b1; };
     std::vector<Chunk> chunks;
     {

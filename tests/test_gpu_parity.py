@@ -502,6 +502,45 @@ def test_driver_cli_with_binary_cache(tmp_path):
     assert np.array_equal(outs[0][0], outs[2][0])
 
 
+def test_driver_cli_pulls_many_chunks_from_the_queue(tmp_path):
+    # the CLI's shared queue with chunks small enough that a single GPU keeps three in flight and retires many:
+    # results land at each batch's own place, with the fast kernels behind it
+    import os
+    import subprocess
+    from conftest import ROOT
+    fb = synth.generic(15, 40, (2, 20), (1, 8), (20, 250), (30, 500), q_rng=(6, 45), foreign_frac=0.2)
+    ref = oracle.run_port(fb)
+    path = str(tmp_path / "in.txt")
+    open(path, "wb").write(fb.to_text())
+    exe = os.path.join(ROOT, "genomicsbench_palisade_b200", "phmm")
+    for fast in ("0", "1"):
+        pr = subprocess.run([exe, "-f", path, "-p", "-l", "2"], capture_output=True, text=True, timeout=300,
+                            env=dict(os.environ, PHMM_CLI_CHUNK_COST="3e6", PHMM_FAST=fast))
+        assert pr.returncode == 0, pr.stderr
+        lines = pr.stdout.strip().split("\n")
+        out = np.array([float(x) for x in lines[:-1]])
+        assert len(out) == fb.n_pairs and np.allclose(out, ref.out, rtol=1e-4, atol=2e-6)
+        n_chunks = int(pr.stderr.split("phmm: ")[1].split(" chunks")[0])
+        assert n_chunks >= 8, pr.stderr
+        assert "%d FP64-rescued" % int(ref.rescued.sum()) in pr.stderr
+
+
+def test_page_locked_caller_buffers():
+    # phmm_host_register: the same call from buffers the caller pinned once gives the same bits
+    fb = synth.generic(19, 10, (5, 40), (2, 9), (20, 250), (30, 500), q_rng=(6, 45), foreign_frac=0.2)
+    eng = phmm.PairHMM(fast=True, chunk_cells=2_000_000)
+    a = eng.compute(fb)
+    o = np.empty(fb.n_pairs)
+    pools = (fb.rs, fb.q, fb.i, fb.d, fb.c, fb.hap, o)
+    eng.pin(*pools)
+    b = eng.compute(fb, out=o).copy()
+    c = eng.compute(fb, out=o).copy()
+    eng.unpin(*pools)
+    d = eng.compute(fb)
+    eng.close()
+    assert np.array_equal(a, b) and np.array_equal(a, c) and np.array_equal(a, d)
+
+
 def test_unmodified_reference_driver_linked_against_libphmm_cuda(tmp_path):
     """INTEGRATION.md section 1 for real: the reference's own driver source
     (tools/GKL/src/examples/PairHMM/PairHMMUnitTest.cpp, compiled unmodified by oracle/build_ref.sh in the
