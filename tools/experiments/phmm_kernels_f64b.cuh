@@ -1,4 +1,7 @@
-// FP64 pair-HMM forward kernel, "column-block wavefront" (sm_100a) -- the fast FP64 rescue path.
+// NOT PART OF THE BUILD: an experiment of round 2, kept for the record (profiles/r2_f64_rescue_register_port.md).
+// It passed the GPU suite when wired in as lookup_f64_f1 and was not faster than phmm_forward_kernel<double, ...>.
+//
+// FP64 pair-HMM forward kernel, "column-block wavefront" (sm_100a).
 //
 // Same computation as phmm_forward_kernel<double, KH, 32, FAST = true> (phmm_kernels.cuh; reference:
 // compute_full_prob_<double>, tools/GKL/src/main/native/pairhmm/avx-pairhmm-template.h:210-346, called for the
