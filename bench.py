@@ -463,6 +463,15 @@ class _Solo:
         self.R.torch.cuda.synchronize()
 
 
+def hbm_peak():
+    """Measured copy bandwidth of this pool's B200s (driver-written MEASURED_PEAKS.json), else the profiling guide's
+    fallback."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6500.0
+
+
 def tile_fill(fb, fast):
     """cells / tile cells of rank 0's plan: the share of the FP32 kernels' row steps that are real read rows (a read
     of R bases occupies kh x lanes rows of its class's register tile; separator columns count as tile cells too)."""
@@ -569,6 +578,8 @@ def main():
                          "peak_nominal": 148 * 128 * 2 * mhz * 1e6 / 1e12, "frac_of_nominal": ach / (148 * 128 * 2 * mhz * 1e6 / 1e12),
                          "traffic": traffic, "traffic_source": traffic_src,
                          "hbm": {"algorithmic_bytes_per_step": int(m.get("h2d", 0) + 8 * fb.n_pairs),
+                                 "achieved_gbs": (m.get("h2d", 0) + 8 * fb.n_pairs) / (m["ms"] * 1e-3) / 1e9,
+                                 "peak_gbs": hbm_peak(),
                                  "note": "inputs as uploaded + 8 B per result; `traffic` = dram__bytes_read.sum + "
                                          "dram__bytes_write.sum over the FP32 launches of one step from the ncu --set full "
                                          "capture named in traffic_source (C2, one GPU, a constant of that capture, not of "
