@@ -385,12 +385,21 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
                 if (ok || n >= bnh) break;
                 n = std::min(bnh, n + (kind == 1 ? 2 : 1));
             }
+            const size_t first = runs[kind].size();
             for (size_t j = 0; j + 1 < cuts.size(); ++j) {
                 int64_t w = 0;
                 for (int k = cuts[j]; k < cuts[j + 1]; ++k) w += fb.hap_len[h0 + k] + SEP_COLS;
                 runs[kind].push_back(Run{b, cuts[j], cuts[j + 1], (int32_t)w});
             }
-            if (kind == 1 && (cuts.size() - 1) % 2 == 1) runs[1].push_back(Run{b, 0, 0, 0});   // idle second half
+            if (kind == 1) {
+                // A task of the haplotype-pair kernels lasts as long as the longer of its two runs.  Runs are whole
+                // haplotypes, so their lengths differ (by kilobases when the haplotypes are that long): pair the
+                // runs of a batch in order of length, not of position -- the two runs of a task need not be adjacent
+                // (C4: FP32 phase 37.5 -> 30.9 ms; C5 -6 %).
+                std::stable_sort(runs[1].begin() + (std::ptrdiff_t)first, runs[1].end(),
+                                 [](const Run &x, const Run &y) { return x.cols > y.cols; });
+                if ((cuts.size() - 1) % 2 == 1) runs[1].push_back(Run{b, 0, 0, 0});   // idle second half (pairs with the shortest)
+            }
         }
     }
 
