@@ -62,7 +62,7 @@ EXPORTS = ["phmm_abi_version", "phmm_device_count", "phmm_create", "phmm_destroy
            "phmm_plan_summary", "phmm_cache_write", "phmm_cache_open", "phmm_gatk_init",
            "phmm_gatk_compute_likelihoods", "phmm_gatk_compute_regions", "phmm_gatk_done",
            "phmm_gatk_last_error", "phmm_gatk_context", "phmm_testdata_parse_buffer",
-           "phmm_testdata_parse_file", "phmm_testdata_expected"]
+           "phmm_testdata_parse_file", "phmm_testdata_expected", "phmm_forward_region_noalloc"]
 LEGACY_EXPORTS = ["_Z11initPairHMMv", "_Z22computelikelihoodsbothP8testcasePdi",
                   "_Z23computelikelihoodsfloatP8testcasePf", "_Z24computelikelihoodsdoubleP8testcasePd",
                   "_ZN11ConvertChar15conversionTableE"]
@@ -92,8 +92,30 @@ def load_library():
         lib.phmm_gatk_done.argtypes = [C.c_void_p]
         lib.phmm_testdata_expected.restype = C.c_int64
         lib.phmm_testdata_expected.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        lib.phmm_forward_region_noalloc.restype = C.c_int
+        lib.phmm_forward_region_noalloc.argtypes = (
+            [C.c_int, C.c_void_p] + [C.c_void_p] * 6 + [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32,
+                                                         C.c_int32, C.c_void_p, C.c_void_p, C.c_char_p, C.c_size_t])
         _lib = lib
     return _lib
+
+
+# stated maxima of phmm_forward_region_noalloc (include/phmm_cuda.h)
+NOALLOC_MAX_READS, NOALLOC_MAX_HAPS, NOALLOC_MAX_PAIRS = 1024, 128, 32768
+NOALLOC_MAX_READ_LEN, NOALLOC_MAX_HAP_BYTES = 255, 65536
+
+
+def forward_region_noalloc(device, stream, d_rs, d_q, d_i, d_d, d_c, d_read_off, n_reads, max_read_len,
+                           d_hap, d_hap_off, n_haps, hap_bytes, d_out, d_rescued=None):
+    """phmm_forward_region_noalloc (no counterpart in the reference; include/phmm_cuda.h): every pointer is a DEVICE
+    address given as an int (e.g. torch.Tensor.data_ptr()), `stream` a cudaStream_t as an int or None.  Queues the
+    work and returns; raises PhmmError with the library's message when a stated maximum is exceeded."""
+    err = C.create_string_buffer(256)
+    rc = load_library().phmm_forward_region_noalloc(
+        device, stream, d_rs, d_q, d_i, d_d, d_c, d_read_off, n_reads, max_read_len, d_hap, d_hap_off, n_haps,
+        hap_bytes, d_out, d_rescued, err, len(err))
+    if rc != 0:
+        raise PhmmError(rc, err.value.decode())
 
 
 def _ptr(a):

@@ -332,6 +332,46 @@ int phmm_get_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d, 
 int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int seg_cols,
                       int64_t *info, uint8_t *pair_cover);
 
+/* ---- allocation-free entry point ----------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * One region = all n_reads x n_haps pairs, computelikelihoodsboth policy (FP32, pairs below MIN_ACCEPTED
+ * again in FP64), through the library's bit-exact kernels.  The call allocates nothing, on the device or
+ * on the host, frees nothing and reads nothing back: the kernels' scratch (probability tables, read
+ * records, coded haplotype stream, task lists, queue heads, FP64-rescue list, raw sums) lives in one
+ * file-scope static __device__ array of PHMM_NOALLOC_SCRATCH_BYTES that every GPU that loads the library
+ * holds until exit (csrc/phmm_noalloc.cu); planning runs on the device.  Inputs and outputs are the
+ * CALLER'S DEVICE buffers on `device`:
+ *   d_rs, d_q, d_i, d_d, d_c   read pools (bases; Phred qualities as the driver normalises them)
+ *   d_read_off[n_reads + 1]    read r = pool bytes [d_read_off[r], d_read_off[r + 1]), 1..max_read_len long
+ *   d_hap, d_hap_off[n_haps+1] haplotype h = d_hap bytes [d_hap_off[h], d_hap_off[h + 1]), ascending;
+ *                              hap_bytes >= d_hap_off[n_haps] - d_hap_off[0]
+ *   d_out[n_reads * n_haps]    log10 likelihoods, read-major (r * n_haps + h)
+ *   d_rescued                  same shape, 1 = pair went through FP64; may be NULL
+ * The work is queued on `cuda_stream` (a cudaStream_t; NULL = the default stream) and the call returns
+ * without waiting.  The first call on a device also sets that device up (cudaGetSymbolAddress of the array,
+ * table upload into it, kernel attributes -- still no allocation) and must not happen under capture.
+ * Sizes beyond the maxima below are refused with PHMM_ERR_TOO_LONG and a message in `err` (may be NULL).
+ * Tables on the device that contradict the stated sizes (a read longer than max_read_len, haplotypes
+ * beyond hap_bytes, offsets not ascending) cannot be reported without a read-back: every result of such a
+ * call is NaN.  All calls on a GPU share the array, which keeps the last call's contents (what must start
+ * at zero is cleared by every call): calls that OVERLAP on one GPU race -- serialise them (one stream, or
+ * events). */
+#define PHMM_NOALLOC_MAX_READS      1024
+#define PHMM_NOALLOC_MAX_HAPS       128
+#define PHMM_NOALLOC_MAX_PAIRS      32768      /* n_reads * n_haps */
+#define PHMM_NOALLOC_MAX_READ_LEN   255
+#define PHMM_NOALLOC_MAX_HAP_BYTES  65536      /* sum of the haplotype lengths */
+#define PHMM_NOALLOC_SCRATCH_BYTES  (3u << 20) /* the static device array, per GPU */
+int phmm_forward_region_noalloc(int device, void *cuda_stream,
+                                const uint8_t *d_rs, const uint8_t *d_q, const uint8_t *d_i,
+                                const uint8_t *d_d, const uint8_t *d_c, const int32_t *d_read_off,
+                                int32_t n_reads, int32_t max_read_len,
+                                const uint8_t *d_hap, const int32_t *d_hap_off, int32_t n_haps,
+                                int32_t hap_bytes, double *d_out, uint8_t *d_rescued,
+                                char *err, size_t err_cap);
+
 #ifdef __cplusplus
 } /* extern "C" */
 #endif
