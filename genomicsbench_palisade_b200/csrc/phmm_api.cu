@@ -588,6 +588,12 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     const size_t upload_extent = (size_t)((uint8_t *)w->d_out - base);
     uint8_t *stage = nullptr;
     if (arena && upload_extent <= Arena::STAGE_MAX) {
+        // the first small chunk of a context gives every slot its staging buffer: a later call whose small first
+        // chunk lands in a slot that never staged would pay the page-locked allocation (1-3 ms) inside its pipeline
+        if (arena->stage_cap == 0)
+            for (Arena &a : ctx->arena)
+                if (a.stage_cap == 0 && cudaMallocHost((void **)&a.stage, Arena::STAGE_MAX) == cudaSuccess) a.stage_cap = Arena::STAGE_MAX;
+                else if (a.stage_cap == 0) { a.stage = nullptr; cudaGetLastError(); }
         if (arena->stage_cap < upload_extent) {
             if (arena->stage) cudaFreeHost(arena->stage);
             arena->stage = nullptr;
@@ -1314,7 +1320,8 @@ extern "C" int phmm_wait(phmm_ctx *ctx, int64_t ticket, phmm_stats *stats)
 }
 
 // Queues one merged set of batches (owned by the caller of this helper until it returns) in a free slot.
-static int submit_merged(phmm_ctx *ctx, const phmm_flat_batches &view, phmm_ctx::Inflight &f, int64_t *ticket)
+static int submit_merged(phmm_ctx *ctx, const phmm_flat_batches &view, phmm_ctx::Inflight &f, int64_t *ticket,
+                         Plan *prebuilt = nullptr)
 {
     f.ticket = ++ctx->next_ticket;
     f.slot = (int)(f.ticket % phmm_ctx::N_SLOTS);
@@ -1322,9 +1329,9 @@ static int submit_merged(phmm_ctx *ctx, const phmm_flat_batches &view, phmm_ctx:
     for (const phmm_ctx::Inflight &g : ctx->inflight)
         if (g.slot == f.slot) { int rc = phmm_wait(ctx, g.ticket, &ctx->retired_stats); if (rc != PHMM_OK) return rc; break; }
     PlanOptions popt = plan_options(ctx);
-    popt.latency = plan_latency(view, popt);
+    if (!prebuilt) popt.latency = plan_latency(view, popt);
     StreamSet &ss = ctx->ss[f.slot];
-    int rc = wl_create(ctx, &view, &ctx->arena[f.slot], ctx->copy_in, &f.w, nullptr, &popt);
+    int rc = wl_create(ctx, &view, &ctx->arena[f.slot], ctx->copy_in, &f.w, prebuilt, &popt);
     if (rc != PHMM_OK) return rc;
     if (cudaEventRecord(ss.ev_uploaded, ctx->copy_in) != cudaSuccess) { ctx->error = "cudaEventRecord failed"; phmm_workload_destroy(f.w); return PHMM_ERR_CUDA; }
     rc = wl_launch(ctx, f.w, ss, ss.ev_uploaded);
@@ -1400,6 +1407,25 @@ extern "C" int phmm_submit_flat(phmm_ctx *ctx, const phmm_flat_request *reqs, in
     m.finish();
     return submit_merged(ctx, m.view, f, ticket);
 }
+
+// Library-internal (phmm_gatk.cpp): a submission whose plan was built ahead of time on a thread of the caller's, so
+// that the thread that owns the context only uploads and launches.  `plan` is moved from.
+namespace phmm {
+PlanOptions context_plan_options(const phmm_ctx *ctx)
+{
+    PlanOptions popt = plan_options(ctx);
+    return popt;
+}
+int submit_planned(phmm_ctx *ctx, const phmm_flat_batches *fb, Plan *plan, double *out, int64_t *ticket)
+{
+    if (!ctx || !fb || !plan || !ticket) return PHMM_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    phmm_ctx::Inflight f;
+    if (plan->n_pairs && !out) { ctx->error = "NULL output"; return PHMM_ERR_ARG; }
+    f.scatter.push_back({out, 0, plan->n_pairs});
+    return submit_merged(ctx, *fb, f, ticket, plan);
+}
+}  // namespace phmm
 
 extern "C" int phmm_submit_pairs(phmm_ctx *ctx, const phmm_pairs_request *reqs, int n_reqs, int64_t *ticket)
 {

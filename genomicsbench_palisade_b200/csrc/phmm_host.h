@@ -75,6 +75,10 @@ int plan_latency(const phmm_flat_batches &fb, const PlanOptions &opt);
 // Builds the plan; on failure returns a PHMM_ERR_* code and fills `err`.
 int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, std::string *err);
 
+// ---- library-internal entry of the asynchronous pipeline (phmm_api.cu), for callers that plan on their own threads
+PlanOptions context_plan_options(const phmm_ctx *ctx);
+int submit_planned(phmm_ctx *ctx, const phmm_flat_batches *fb, Plan *plan, double *out, int64_t *ticket);
+
 // ---- cost model of the scheduler (phmm_cost.cpp) -------------------------------------------------
 // Device time of a read against one haplotype column = lanes x (rows per thread + step_rows) row steps of its
 // kernel class; an FP64 row step costs f64_row_cost FP32 ones, a row step of the bit-exact FP32 kernels (two reads

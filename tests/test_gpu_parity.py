@@ -478,6 +478,51 @@ def test_gatk_shaped_api():
         raise phmm.PhmmError(rc, "use_fpga") if rc else AssertionError("use_fpga accepted")
 
 
+_GATK_LARGE_CALL = r"""
+import sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from genomicsbench_palisade_b200 import phmm, synth
+sys.path.insert(0, sys.argv[1] + "/tests")
+from test_gpu_parity import _regions
+fb = synth.generic(synth.SEED0 + 61, 224, (40, 120), (4, 12), (100, 250), (200, 500), foreign_frac=0.03)
+regs = _regions(fb)
+regs.insert(100, ([], [b"ACGT"]))                      # an empty region in the middle of a group
+eng = phmm.PairHMM(fast=False)
+want = eng.compute(fb)
+eng.close()
+g = phmm.GatkPairHMM()
+got = np.concatenate(g.compute_regions(regs))
+assert got.shape == want.shape and np.array_equal(got.view(np.uint64), want.view(np.uint64)), "results differ"
+# a malformed region late in the call: reported, nothing left in flight, the next call is fine
+bad = list(regs)
+bad[200] = ([(b"", b"", b"", b"", b"")], [b"ACGT"])
+try:
+    g.compute_regions(bad)
+    raise SystemExit("empty read accepted")
+except phmm.PhmmError as e:
+    assert e.code == 2, e
+again = np.concatenate(g.compute_regions(regs))
+assert np.array_equal(again.view(np.uint64), want.view(np.uint64))
+g.done()
+print("OK", fb.n_pairs, fb.n_cells)
+"""
+
+
+def test_gatk_large_call_is_staged_in_groups_under_the_kernels():
+    # hundreds of regions in one phmm_gatk_compute_regions call: groups of regions staged by helper threads while
+    # the previous groups compute (phmm_gatk.cpp: compute_regions_pipelined); same bits as phmm_compute_flat
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    env = dict(os.environ, PHMM_TRACE="1")
+    pr = subprocess.run([sys.executable, "-c", _GATK_LARGE_CALL, ROOT], capture_output=True, text=True, timeout=600, env=env)
+    assert pr.returncode == 0, pr.stderr[-3000:]
+    assert pr.stdout.strip().startswith("OK")
+    assert "gatk pipelined call" in pr.stderr, "the large call did not take the pipelined path"
+
+
 def test_driver_cli_with_binary_cache(tmp_path):
     # the rewritten driver: text input, then the same input mapped from its binary cache
     import os

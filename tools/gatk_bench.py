@@ -75,7 +75,9 @@ def main():
         if G == 1:
             groups = groups[:256]                      # latency sample
         packed = [marshal(gr) for gr in groups]
-        for cg, _, _ in packed[:2]:                    # warm-up (arenas, module load)
+        # warm-up (arenas, module load; large calls: the staging pools of the pipelined path are allocated by the first
+        # such call and page-locked by the second, ~20 ms once per handle)
+        for cg, _, _ in (packed[:2] if G < 256 else packed + packed + packed[:1]):
             g._check(g.lib.phmm_gatk_compute_regions(g._h, cg, C.c_int64(len(cg))))
         lat = []
         t0 = time.perf_counter()
