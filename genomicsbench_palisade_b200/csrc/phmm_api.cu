@@ -707,6 +707,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     pf.guard = w->d_guard; pf.guard_count = w->d_ints + INTS_GUARD;
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) pf.resc_off[k] = w->resc_off[k];
     pf.mode = mode;
+    pf.resc_force = P.resc_force;
     KernelParams<double> pd;
     memset(&pd, 0, sizeof pd);
     pd.rs = pf.rs; pd.q = pf.q; pd.i = pf.i; pd.d = pf.d; pd.c = pf.c;
@@ -715,6 +716,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     pd.init_const = t.init_d; pd.log10_init = t.log10_init_d;
     pd.out = w->d_out; pd.raw32 = w->d_raw32; pd.raw64 = w->d_raw64; pd.rescued = w->d_rescued;
     pd.mode = mode;
+    pd.resc_force = P.resc_force;
     // fast FP64 kernels hand non-finite sums to the exact ones through the (by then consumed) guard list storage
     pd.guard = fast64 ? w->d_guard : nullptr; pd.guard_count = w->d_ints + INTS_GUARD64;
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) pd.resc_off[k] = w->resc_off[k];
@@ -1011,6 +1013,7 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
     size_t next_job = 0, consumed = 0;
     PlanOptions popt = plan_options(ctx);
     popt.latency = plan_latency(*fb, popt);        // one decision for the whole call, not one per chunk
+    popt.one_class = plan_one_class(*fb, popt);
     static const int n_planners_env = getenv("PHMM_PLANNERS") ? atoi(getenv("PHMM_PLANNERS")) : 0;
     const int n_planners = chunks.size() > 1
         ? std::max(1, std::min<int>({n_planners_env > 0 ? n_planners_env : 3, (int)chunks.size(),
@@ -1329,7 +1332,7 @@ static int submit_merged(phmm_ctx *ctx, const phmm_flat_batches &view, phmm_ctx:
     for (const phmm_ctx::Inflight &g : ctx->inflight)
         if (g.slot == f.slot) { int rc = phmm_wait(ctx, g.ticket, &ctx->retired_stats); if (rc != PHMM_OK) return rc; break; }
     PlanOptions popt = plan_options(ctx);
-    if (!prebuilt) popt.latency = plan_latency(view, popt);
+    if (!prebuilt) { popt.latency = plan_latency(view, popt); popt.one_class = plan_one_class(view, popt); }
     StreamSet &ss = ctx->ss[f.slot];
     int rc = wl_create(ctx, &view, &ctx->arena[f.slot], ctx->copy_in, &f.w, prebuilt, &popt);
     if (rc != PHMM_OK) return rc;

@@ -33,6 +33,8 @@ struct PlanOptions {
     int force_kh = 0, force_lanes = 0;   // debugging / benchmarking: pin the kernel class
     int hp = 0;               // 1 = plan haplotype-pair tasks (fast FP32 kernels) for single-pass reads
     int latency = -1;         // 1 = plan for the latency of a small call (32 lanes per read, one haplotype per run); -1 = decide from the size
+    int one_class = -1;       // latency plans whose tasks fit the device in one wave: > 0 = every read in the 32-lane class of this
+                              // height, all rescue / guard work in that scalar class; 0 = classes by read length; -1 = decide from the input
 };
 
 struct ClassPlan {
@@ -65,6 +67,7 @@ struct Plan {
     std::vector<Segment> segments;
     int64_t pool_len = 0;                // sum of segment lengths
     int64_t resc_cap[MAX_KH_SCALAR + 1]; // pairs whose read falls in each scalar class
+    int resc_force = 0;                  // > 0: one-wave call, all rescue / guard work in this scalar class (KernelParams::resc_force)
     int max_rslen = 0, max_haplen = 0;
     int long_max_cols = 0;               // longest run handed to a multi-pass kernel (0 = none)
 };
@@ -72,6 +75,7 @@ struct Plan {
 // Chooses the kernel class for a read length; returns false when no single-pass class fits.
 bool choose_class(int rslen, const PlanOptions &opt, KClass *kc);
 int plan_latency(const phmm_flat_batches &fb, const PlanOptions &opt);
+int plan_one_class(const phmm_flat_batches &fb, const PlanOptions &opt);     // opt.latency resolved; like plan_latency, once per call
 // Builds the plan; on failure returns a PHMM_ERR_* code and fills `err`.
 int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt, Plan *plan, std::string *err);
 

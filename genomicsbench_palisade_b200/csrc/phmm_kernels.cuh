@@ -131,6 +131,13 @@ __host__ __device__ __forceinline__ int rescue_class(int rslen)
     return kh <= MAX_KH_SCALAR ? kh : 0;
 }
 
+// the list a kernel appends rescue / guard work of a read to
+template <typename T>
+__device__ __forceinline__ int list_class(const KernelParams<T> &P, int rslen)
+{
+    return P.resc_force > 0 ? P.resc_force : rescue_class(rslen);
+}
+
 // ------------------------------------------------------------------------------------------
 // Result of one (read, haplotype): policy of computelikelihoodsboth (IntelPairHmmCSource.cpp:69-82).
 // ------------------------------------------------------------------------------------------
@@ -172,7 +179,7 @@ __device__ __forceinline__ void resc_flush(const KernelParams<float> &P, RescRun
     nt.out0 = pr.out0;
     nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
     nt.nh = pr.nh;
-    const int ci = rescue_class(rslen);
+    const int ci = list_class(P, rslen);
     const int k = atomicAdd(&P.resc_count[ci], 1);
     P.resc[P.resc_off[ci] + k] = nt;
     atomicAdd(P.resc_pairs, pr.nh);
@@ -206,7 +213,7 @@ __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float 
         nt.out0 = out_rel;
         nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
         nt.nh = 1;
-        const int ci = rescue_class(rslen);
+        const int ci = list_class(P, rslen);
         if (redo) {
             int k = atomicAdd(&P.guard_count[ci], 1);
             P.guard[P.resc_off[ci] + k] = nt;
@@ -237,7 +244,7 @@ __device__ __forceinline__ void emit_result(const KernelParams<double> &P, doubl
         nt.out0 = out_rel;
         nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
         nt.nh = 1;
-        const int ci = rescue_class(rslen);
+        const int ci = list_class(P, rslen);
         const int k = atomicAdd(&P.guard_count[ci], 1);
         P.guard[P.resc_off[ci] + k] = nt;
         return;

@@ -290,7 +290,7 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
                                         // (reads of the multi-pass FP64 class keep one pair per task: its boundary-row
                                         // scratch is sized for one haplotype)
                                         if (pr.nh > 0 && pr.nh < RESC_RUN_HAPS && pr.ncols + hl + SEP_COLS <= RESC_RUN_COLS &&
-                                            rescue_class(R) != 0) {
+                                            list_class(P, R) != 0) {
                                             pr.nh += 1;
                                             pr.ncols += hl + SEP_COLS;
                                         } else {
@@ -311,7 +311,7 @@ phmm_forward_hp_kernel(const KernelParams<float> P)
                                             nt.out0 = out0[h] + jh[h];
                                             nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
                                             nt.nh = 1;
-                                            const int ci = rescue_class(R);
+                                            const int ci = list_class(P, R);
                                             const int k = atomicAdd(&P.guard_count[ci], 1);
                                             P.guard[P.resc_off[ci] + k] = nt;
                                         }

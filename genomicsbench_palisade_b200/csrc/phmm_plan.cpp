@@ -78,6 +78,30 @@ int plan_latency(const phmm_flat_batches &fb, const PlanOptions &opt)
     return (t < limit && cells < 3e9) ? 1 : 0;
 }
 
+// One-wave calls (one active region, a few): one kernel class.  When the tasks of a latency-planned call fit the
+// device in one wave, the call lasts as long as its longest task whichever classes the shorter reads run in -- but
+// every class is a launch of its own in each of the phases (FP32, guard band, FP64 rescue), with its fork and join
+// events, and a single-region call is mostly launch overhead.  All reads then take the 32-lane class of the longest
+// read, and all rescue / guard work goes to that read's scalar class.  Returns that class's height, 0 = no.  Like the
+// latency decision it is taken once per host-buffer call, so a pair's result does not depend on the cut into chunks.
+int plan_one_class(const phmm_flat_batches &fb, const PlanOptions &opt)
+{
+    if (opt.one_class >= 0) return opt.one_class;
+    if (opt.latency != 1 || opt.force_kh > 0 || fb.n_reads <= 0 || !fb.read_len || !fb.batch_num_reads || !fb.batch_num_haps) return 0;
+    int max_rslen = 0;
+    for (int64_t r = 0; r < fb.n_reads; ++r) max_rslen = std::max(max_rslen, fb.read_len[r]);
+    if (max_rslen < 1 || max_rslen + 1 > 32 * MAX_KH_SCALAR) return 0;
+    const bool hp = opt.hp && opt.precision != 2;
+    const int g = (hp || opt.precision == 2) ? 1 : 2;          // reads per 32-lane task
+    int64_t t = 0;
+    for (int64_t b = 0; b < fb.n_batches; ++b) {
+        const int64_t nr = std::max(fb.batch_num_reads[b], 0), nh = std::max(fb.batch_num_haps[b], 0);
+        t += ((nr + g - 1) / g) * (hp ? (nh + 1) / 2 : nh);     // one haplotype per run
+        if (t > opt.resident_warps / 2) return 0;
+    }
+    return (max_rslen + 1 + 31) / 32;
+}
+
 int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *plan, std::string *err)
 {
     char msg[256];
@@ -112,6 +136,12 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
         if (fb.read_off[r] < 0) return fail(PHMM_ERR_ARG, "negative read offset");
         if (r && fb.read_off[r] < fb.read_off[r - 1]) sorted = false;
         P.max_rslen = std::max(P.max_rslen, len);
+    }
+    if (opt.one_class < 0) opt.one_class = plan_one_class(fb, opt);
+    if (opt.one_class > 0 && opt.force_kh <= 0) {
+        opt.force_kh = opt.one_class;
+        opt.force_lanes = 32;
+        P.resc_force = opt.one_class;
     }
     // ---- pool segments: merge the reads' byte ranges (gaps up to 64 bytes are carried along) so that
     //      only referenced data is uploaded, whatever else the caller's pools hold ------------------
@@ -284,7 +314,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
                 rr.out_base = out0 + (int64_t)k * bnh;
                 by_class[read_class[r]].push_back((int32_t)r);
                 P.n_cells += (int64_t)rr.len * sum_h;
-                P.resc_cap[scalar_class_of(rr.len)] += bnh;
+                P.resc_cap[P.resc_force > 0 ? P.resc_force : scalar_class_of(rr.len)] += bnh;
             }
             int prev = -1;
             for (size_t oi = 0; oi < ncls; ++oi) {

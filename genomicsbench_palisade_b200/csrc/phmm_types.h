@@ -137,6 +137,8 @@ struct KernelParams {
     int32_t *resc_pairs;                 // pairs in those tasks (a task may hold a run of rescued haplotypes)
     int32_t resc_off[MAX_KH_SCALAR + 1]; // start of each class's list inside resc / guard
     int32_t mode;                        // PHMM_OPT_PRECISION
+    int32_t resc_force;                  // > 0: every rescue / guard task goes to this scalar class's list (one-wave calls,
+                                         // Plan::resc_force); 0: by read length
     Task *guard;                         // guard-band list (fast kernel only)
     int32_t *guard_count;
     T *scratch;                          // multi-pass kernels: per-warp boundary rows
