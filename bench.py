@@ -493,6 +493,19 @@ def sw_block(R, no_cpu):
     return sw_bench.measure(a, device=R.local, flush=R.flush_buf, cpu_seconds=4.0)
 
 
+def gatk_block(R, no_cpu):
+    """tools/gatk_bench.py's measurement of SURVEY.md 8f row 1 (the GATK-shaped batch API, host holders in, host
+    likelihoods out) as a block of this line: the entry's default bit-exact kernels at 1 / 16 / 256 / 1024 regions
+    per call with the reference (FTZ on, as its JNI entry sets it) one region per call beside them, and the opt-in
+    fast kernels for the single-region and the all-regions call."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gatk_bench
+    b = gatk_bench.measure(1024, "exact", no_cpu, device=R.local)
+    f = gatk_bench.measure(1024, "fast", True, device=R.local, sizes=(1, 0))
+    b["fast_kernels"] = f["groups"]
+    return b
+
+
 def ncu_traffic():
     """DRAM bytes per step of the FP32 launches (dram__bytes_read.sum + dram__bytes_write.sum) from the newest
     committed ncu --set full capture of this benchmark (C2, one GPU); None when there is none."""
@@ -529,9 +542,10 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.configs is None:
-        args.configs = "c1,c3,c4,c5,sw" if args.workload == "c2" else "none"
-    subs = [c for c in args.configs.split(",") if c and c not in ("none", "sw")]
+        args.configs = "c1,c3,c4,c5,sw,gatk" if args.workload == "c2" else "none"
+    subs = [c for c in args.configs.split(",") if c and c not in ("none", "sw", "gatk")]
     with_sw = "sw" in args.configs.split(",")
+    with_gatk = "gatk" in args.configs.split(",")
 
     if args.impl == "reference":
         reference_arm(args, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
@@ -625,6 +639,9 @@ def main():
     if with_sw and rank == 0:
         # SURVEY.md 8f row 3 (GKL Smith-Waterman with backtrack, libsw_cuda.so): one GPU, not sharded
         line["sw"] = sw_block(R, args.no_cpu)
+    if with_gatk and rank == 0:
+        # SURVEY.md 8f row 1 (GATK native-bindings-shaped batch API): one GPU, host buffers in and out
+        line["gatk"] = gatk_block(R, args.no_cpu)
     R.barrier()
     R.close()
     if rank == 0:

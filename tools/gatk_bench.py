@@ -47,6 +47,13 @@ def main():
     ap.add_argument("--kernels", default="exact", choices=["exact", "fast"],
                     help="exact = the entry's default (bit-exact kernels); fast = the opt-in (PHMM_OPT_FP32/FP64_KERNEL 1)")
     a = ap.parse_args()
+    print(json.dumps(measure(a.regions, a.kernels, a.no_cpu)))
+
+
+def measure(n_regions=1024, kernels="exact", no_cpu=False, device=0, sizes=(1, 16, 256, 0)):
+    """sizes: regions per call, 0 = all in one call."""
+    import types
+    a = types.SimpleNamespace(regions=n_regions, kernels=kernels, no_cpu=no_cpu)
     # active regions: 20-120 reads of 100-250 bp x 2-12 haplotypes of 200-500 bp
     fb = synth.generic(synth.SEED0 + 60, a.regions, (20, 120), (2, 12), (100, 250), (200, 500), foreign_frac=0.03,
                        name="gatk-regions")
@@ -54,7 +61,7 @@ def main():
     cells = fb.batch_cells.astype(np.int64)
     out = {"metric": "GATK-shaped batch API (phmm_gatk_*), end to end", "regions": len(regs), "pairs": fb.n_pairs,
            "cells": int(cells.sum()), "mean_pairs_per_region": fb.n_pairs / len(regs), "kernels": a.kernels, "groups": []}
-    g = phmm.GatkPairHMM(fast=(a.kernels == "fast"))
+    g = phmm.GatkPairHMM(device=device, fast=(a.kernels == "fast"))
     # ctypes marshalling of thousands of small byte strings is Python time, not library time: build the C
     # holder arrays once per group outside the timed region
     import ctypes as C
@@ -70,7 +77,7 @@ def main():
         return cg, keep, outs
 
     ref_out = None
-    for G in (1, 16, 256, len(regs)):
+    for G in [x if x else len(regs) for x in sizes]:
         groups = [regs[k:k + G] for k in range(0, len(regs), G)]
         if G == 1:
             groups = groups[:256]                      # latency sample
@@ -112,7 +119,7 @@ def main():
                                "ms_per_region": 1e3 * dt / len(subs),
                                "sample": "first %d regions, one call per region, OpenMP over the pairs of a region" % len(subs),
                                "gpu_results_within_tolerance": ok}
-    print(json.dumps(out))
+    return out
 
 
 if __name__ == "__main__":
