@@ -35,7 +35,7 @@ def _existing(eng, fb):
     return out, resc
 
 
-def _noalloc(torch, fb, max_read_len=None, lie_about_reads=False):
+def _noalloc(torch, fb, max_read_len=None):
     rs, q, i, d, c, roff, hap, hoff = _packed(fb)
     dev = [torch.from_numpy(a).cuda() for a in (rs, q, i, d, c, roff, hap, hoff)]
     n_reads, n_haps = len(fb.read_len), len(fb.hap_len)
@@ -105,3 +105,45 @@ def test_noalloc_rejects_sizes_beyond_the_maximum():
     with pytest.raises(phmm.PhmmError) as e:
         phmm.forward_region_noalloc(0, None, 256, 256, 256, 256, 256, None, 8, 100, 256, 256, 4, 1000, 256)
     assert e.value.code == 1
+
+
+@pytest.mark.gpu
+def test_noalloc_entry_point_under_cuda_graph_capture():
+    """The reason the entry point exists: it can be captured (no allocation, no synchronisation, nothing read back) and
+    the graph replayed on new contents of the same buffers."""
+    import torch
+    fbs = [_region(305, 40, 9, (60, 200), (100, 300)), _region(306, 40, 9, (60, 200), (100, 300))]
+    eng = phmm.PairHMM(device=0, fast=False)
+    want = [_existing(eng, fb) for fb in fbs]
+    eng.close()
+    packed = [_packed(fb) for fb in fbs]
+    # fixed-size device buffers (the graph bakes the pointers and the host-side sizes in): sized for the larger region
+    sizes = [max(len(p[k]) for p in packed) for k in range(8)]
+    dev = [torch.zeros(n + 1, dtype=torch.from_numpy(packed[0][k]).dtype, device="cuda") for k, n in enumerate(sizes)]
+    n_reads, n_haps = 40, 9
+    out = torch.zeros(n_reads * n_haps, dtype=torch.float64, device="cuda")
+    resc = torch.zeros(n_reads * n_haps, dtype=torch.uint8, device="cuda")
+    p = [t.data_ptr() for t in dev]
+    mrl, hap_cap = 200, sizes[6]
+
+    def load(k):
+        for t, a in zip(dev, packed[k]):
+            t[:len(a)].copy_(torch.from_numpy(a))
+
+    def call(stream):
+        phmm.forward_region_noalloc(0, stream, p[0], p[1], p[2], p[3], p[4], p[5], n_reads, mrl, p[6], p[7], n_haps,
+                                    hap_cap, out.data_ptr(), resc.data_ptr())
+
+    load(0)
+    call(None)                      # the first call on a device sets it up: outside capture
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        call(torch.cuda.current_stream().cuda_stream)
+    for k in (1, 0, 1):
+        load(k)
+        out.zero_()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy().view(np.uint64), want[k][0].view(np.uint64))
+        assert np.array_equal(resc.cpu().numpy(), want[k][1])
