@@ -82,6 +82,20 @@ def test_fast_plan_pairs_runs_of_haplotypes():
                 assert lanes in (8, 16, 32) and 1 <= kh <= 16 and vl == 2 and ntasks > 0
 
 
+def test_one_wave_calls_are_planned_with_one_class():
+    # a call whose tasks fit the device in one wave (one active region): every read in the 32-lane class of the
+    # longest read -- one launch per phase instead of one per class (phmm_plan.cpp: plan_one_class)
+    region = synth.generic(synth.SEED0 + 71, 1, (60, 60), (8, 8), (100, 250), (200, 500))
+    assert len(set(int(x + 32) // 32 for x in region.read_len)) > 2          # the reads span several class heights
+    for fast in (False, True):
+        s = phmm.plan_summary(region, fast=fast)
+        assert (s["cover"] == 1).all()
+        assert [(kh, lanes) for kh, lanes, _, _ in s["classes"]] == [((int(region.read_len.max()) + 32) // 32, 32)]
+    # hundreds of regions in one call do not fit one wave: classes by read length again
+    many = synth.generic(synth.SEED0 + 72, 64, (40, 80), (6, 10), (100, 250), (200, 500))
+    assert len(phmm.plan_summary(many, fast=True)["classes"]) > 1 and len(phmm.plan_summary(many)["classes"]) > 1
+
+
 def test_plan_rejects_bad_input():
     with pytest.raises(phmm.PhmmError) as e:
         phmm.plan_summary(from_lists([([(b"", b"", b"", b"", b"")], [b"ACGT"])]))
