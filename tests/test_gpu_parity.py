@@ -506,6 +506,14 @@ except phmm.PhmmError as e:
 again = np.concatenate(g.compute_regions(regs))
 assert np.array_equal(again.view(np.uint64), want.view(np.uint64))
 g.done()
+# useDoublePrecision (IntelPairHmm.cc:123-124) through the same pipeline: every pair in FP64
+eng = phmm.PairHMM(precision=phmm.DOUBLE_ONLY, fast=False)
+want64 = eng.compute(fb)
+eng.close()
+g = phmm.GatkPairHMM(use_double=True)
+got64 = np.concatenate(g.compute_regions(regs))
+g.done()
+assert np.array_equal(got64.view(np.uint64), want64.view(np.uint64)), "FP64-only results differ"
 print("OK", fb.n_pairs, fb.n_cells)
 """
 
