@@ -79,6 +79,7 @@ struct Arena {
 struct phmm_ctx {
     int device = 0;
     int sm_count = 0;
+    float spec_band = 0.015625f;   // FP64-first decision band (relative half-width, PHMM_SPEC_BAND: tests widen it)
     int canary = 0;           // PHMM_CANARY=1: red zones behind every device buffer, checked after each run
     // slot 0 also serves the device-resident workload API; the host-buffer entry points pipeline
     // chunks of batches through all slots (plan + upload of one chunk under the kernels of the others)
@@ -142,6 +143,12 @@ struct phmm_workload {
     Task *d_tasks = nullptr;
     HTask *d_htasks = nullptr;
     Task *d_resc = nullptr, *d_guard = nullptr;
+    // FP64-first reads (Plan::spec_tasks): their tasks as uploaded (copied to the heads of the rescue lists on the
+    // device), and the list of pairs inside the decision band (KernelParams::spec_list)
+    Task *d_spec_tasks = nullptr, *d_spec = nullptr;
+    int32_t spec_ntasks[MAX_KH_SCALAR + 1] = {0}, spec_off[MAX_KH_SCALAR + 1] = {0};
+    int64_t spec_pairs = 0, spec_cells = 0;
+    int64_t last_spec_direct = 0;
     int32_t *d_ints = nullptr;        // [0..63] queue heads, [64..] ntasks per class, resc/guard counts
     double *d_out = nullptr, *d_raw64 = nullptr;
     float *d_raw32 = nullptr;
@@ -160,14 +167,18 @@ struct phmm_workload {
 namespace {
 
 // layout of phmm_workload::d_ints
-const int INTS_COUNTER = 0;                       // one queue head per launch: [0, MAX_STEP_LAUNCHES) for the step,
-const int MAX_STEP_LAUNCHES = 64 - (MAX_KH_SCALAR + 1);   //   the last MAX_KH_SCALAR + 1 for the bit-exact FP64 re-run of wl_finish
-const int INTS_NTASKS = 64;                       // per FP32 class
-const int INTS_RESC = 128;                        // [MAX_KH_SCALAR + 1]
-const int INTS_GUARD = 128 + 16;
-const int INTS_GUARD64 = 128 + 32;                // fast FP64 kernels: non-finite sums, re-run by the exact FP64 kernel
-const int INTS_RESC_PAIRS = 128 + 48;             // pairs in the rescue lists (a task of the fast kernels holds a run of haplotypes)
-const int INTS_TOTAL = 192;
+const int INTS_COUNTER = 0;                       // one queue head per launch: [0, MAX_STEP_LAUNCHES) for the step, then
+const int COUNTER_SLOTS = 96;                     //   MAX_KH_SCALAR + 1 for the bit-exact FP64 re-run of wl_finish and as many for
+const int MAX_STEP_LAUNCHES = COUNTER_SLOTS - 2 * (MAX_KH_SCALAR + 1);   //   its bit-exact FP32 pass over the FP64-first band list
+const int SPEC_FIX_SLOT = MAX_STEP_LAUNCHES + MAX_KH_SCALAR + 1;
+const int INTS_NTASKS = 96;                       // per FP32 class (64)
+const int INTS_RESC = 160;                        // [MAX_KH_SCALAR + 1]
+const int INTS_GUARD = 160 + 16;
+const int INTS_GUARD64 = 160 + 32;                // fast FP64 kernels: non-finite sums, re-run by the exact FP64 kernel
+const int INTS_RESC_PAIRS = 160 + 48;             // pairs in the rescue lists (a task of the fast kernels holds a run of haplotypes)
+const int INTS_SPEC = 160 + 49;                   // FP64-first: [9] band-list tasks per class, [+9] rescued as predicted, [+10] finalised in float
+const int INTS_LISTS = 64;                        // ints from INTS_RESC on that a step clears and wl_finish reads back
+const int INTS_TOTAL = 224;
 
 #define CUDA_TRY(ctx, expr)                                                                   \
     do {                                                                                      \
@@ -267,6 +278,7 @@ extern "C" int phmm_create(int device, phmm_ctx **out)
     if (const char *s = getenv("PHMM_FORCE_CLASS")) sscanf(s, "%d,%d", &ctx->force_kh, &ctx->force_lanes);
     if (const char *s = getenv("PHMM_NO_HP")) ctx->no_hp = atoi(s);
     if (const char *s = getenv("PHMM_CANARY")) ctx->canary = atoi(s);
+    if (const char *s = getenv("PHMM_SPEC_BAND")) ctx->spec_band = (float)atof(s);
     if (const char *s = getenv("PHMM_CHUNK_CELLS")) ctx->chunk_cells = atoll(s);
     auto bail = [&](const char *what, cudaError_t err) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
@@ -442,6 +454,7 @@ static PlanOptions plan_options(const phmm_ctx *ctx)
     o.resident_warps = ctx->sm_count * 16;
     o.latency = ctx->plan_mode == 0 ? -1 : ctx->plan_mode - 1;
     o.hp = (ctx->fp32_fast && ctx->precision != 2 && !ctx->no_hp) ? 1 : 0;
+    o.spec = (o.hp && ctx->precision == 0 && spec_enabled()) ? -1 : 0;
     return o;
 }
 
@@ -516,6 +529,18 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
         w->scratch_blocks = ctx->sm_count * 8 / WARPS_PER_BLOCK;     // eight warps per SM
     }
 
+    // FP64-first tasks and the band list of their pairs
+    int64_t n_spec_tasks = 0, spec_total = 0;
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) {
+        if (spec_total + P.spec_cap[k] > INT32_MAX) { ctx->error = "workload too large for one device (FP64-first list)"; return fail(PHMM_ERR_ARG); }
+        w->spec_ntasks[k] = (int32_t)P.spec_tasks[k].size();
+        w->spec_off[k] = (int32_t)spec_total;
+        n_spec_tasks += w->spec_ntasks[k];
+        spec_total += P.spec_cap[k];
+    }
+    w->spec_pairs = P.spec_pairs;
+    w->spec_cells = P.spec_cells;
+
     // ---- one allocation, carved into 256-byte aligned pieces ------------------------------------
     const size_t np = (size_t)std::max<int64_t>(1, P.n_pairs);
     struct Piece { void **ptr; size_t bytes; const char *name; };
@@ -529,6 +554,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
         {(void **)&w->d_reads, P.reads.size() * sizeof(ReadRec), "reads"},
         {(void **)&w->d_tasks, (size_t)ntasks * sizeof(Task), "tasks"},
         {(void **)&w->d_htasks, (size_t)nhtasks * sizeof(HTask), "htasks"},
+        {(void **)&w->d_spec_tasks, (size_t)n_spec_tasks * sizeof(Task), "FP64-first tasks"},
         {(void **)&w->d_ints, INTS_TOTAL * sizeof(int32_t), "ints"},
         {(void **)&w->d_out, np * sizeof(double), "out"},
         {(void **)(host_coded ? &w->d_unused : &w->d_stream), host_coded ? 0 : (size_t)P.stream_len, "haplotype stream"},
@@ -537,6 +563,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
         {(void **)&w->d_rescued, np, "rescued"},
         {(void **)&w->d_resc, need_resc ? (size_t)tot * sizeof(Task) : 0, "rescue list"},
         {(void **)&w->d_guard, need_resc ? (size_t)tot * sizeof(Task) : 0, "guard list"},
+        {(void **)&w->d_spec, (size_t)spec_total * sizeof(Task), "FP64-first band list"},
         {(void **)&w->d_scratch, (size_t)(w->scratch_stride * w->scratch_blocks * WARPS_PER_BLOCK) * sizeof(double), "scratch"},
     };
     const size_t red = ctx->canary ? 256 : 0;
@@ -629,10 +656,28 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
         WL_TRY(put(w->d_htasks + w->classes[c].task_off, P.classes[c].htasks.data(), P.classes[c].htasks.size() * sizeof(HTask)));
         h2d += (int64_t)P.classes[c].tasks.size() * sizeof(Task) + (int64_t)P.classes[c].htasks.size() * sizeof(HTask);
     }
+    {
+        int64_t at = 0;
+        for (int k = 0; k <= MAX_KH_SCALAR; ++k) {
+            WL_TRY(put(w->d_spec_tasks + at, P.spec_tasks[k].data(), P.spec_tasks[k].size() * sizeof(Task)));
+            at += w->spec_ntasks[k];
+            h2d += (int64_t)P.spec_tasks[k].size() * sizeof(Task);
+        }
+    }
     // (copies from pageable host memory return once the source has been staged, so the plan's
     // vectors and `ints` may be released right after)
     WL_TRY(put(w->d_ints, ints, sizeof ints));
     if (stage) WL_TRY(cudaMemcpyAsync(base, stage, upload_extent, cudaMemcpyHostToDevice, up));
+    {
+        // the FP64-first tasks are the heads of the rescue lists; the kernels append behind them
+        int64_t at = 0;
+        for (int k = 0; k <= MAX_KH_SCALAR; ++k) {
+            if (w->spec_ntasks[k])
+                WL_TRY(cudaMemcpyAsync(w->d_resc + w->resc_off[k], w->d_spec_tasks + at, (size_t)w->spec_ntasks[k] * sizeof(Task),
+                                       cudaMemcpyDeviceToDevice, up));
+            at += w->spec_ntasks[k];
+        }
+    }
     // the haplotype stream: zero (separator columns, alignment gaps, slack), then the code bytes from the raw bases
     if (!host_coded) WL_TRY(cudaMemsetAsync(w->d_stream, 0, (size_t)P.stream_len, up));
     if (!host_coded && !P.hap_src.empty()) {
@@ -652,6 +697,7 @@ static int wl_create(phmm_ctx *ctx, const phmm_flat_batches *fb, Arena *arena, c
     std::vector<HapSrc>().swap(P.hap_src);
     std::vector<uint8_t>().swap(P.stream);
     for (auto &cp : P.classes) { std::vector<Task>().swap(cp.tasks); std::vector<HTask>().swap(cp.htasks); }
+    for (auto &v : P.spec_tasks) std::vector<Task>().swap(v);
     *out = w;
     return PHMM_OK;
 }
@@ -674,7 +720,10 @@ extern "C" int phmm_workload_create(phmm_ctx *ctx, const phmm_flat_batches *fb, 
 // records the timing events.  Does not wait.
 // fallback64 == nullptr: the whole step.  Otherwise only the rare last phase: counts per class of pairs whose
 // fast FP64 sum was non-finite (read back by wl_finish), re-run by the bit-exact FP64 kernels.
-static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t wait_for, const int32_t *fallback64 = nullptr)
+// specfix: counts per class of FP64-first pairs inside the decision band (KernelParams::spec_list), decided by the
+// bit-exact FP32 kernel in mode 3.
+static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t wait_for, const int32_t *fallback64 = nullptr,
+                     const int32_t *specfix = nullptr)
 {
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ss.main;
@@ -690,9 +739,12 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     }
 
     // queue heads and list counters back to zero
-    if (!fallback64) {
-        CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_COUNTER, 0, 64 * sizeof(int32_t), st));
-        CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_RESC, 0, 64 * sizeof(int32_t), st));
+    if (!fallback64 && !specfix) {
+        CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_COUNTER, 0, COUNTER_SLOTS * sizeof(int32_t), st));
+        CUDA_TRY(ctx, cudaMemsetAsync(w->d_ints + INTS_RESC, 0, INTS_LISTS * sizeof(int32_t), st));
+        // the rescue lists start with the FP64-first tasks the planner put there
+        if (w->spec_pairs > 0)
+            CUDA_TRY(ctx, cudaMemcpyAsync(w->d_ints + INTS_RESC, w->spec_ntasks, sizeof w->spec_ntasks, cudaMemcpyHostToDevice, st));
     }
 
     KernelParams<float> pf;
@@ -717,6 +769,10 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     pd.out = w->d_out; pd.raw32 = w->d_raw32; pd.raw64 = w->d_raw64; pd.rescued = w->d_rescued;
     pd.mode = mode;
     pd.resc_force = P.resc_force;
+    pd.spec_list = w->d_spec; pd.spec_count = w->d_ints + INTS_SPEC;
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) pd.spec_off[k] = w->spec_off[k];
+    pd.log10_init32 = t.log10_init_f;
+    pd.spec_band = ctx->spec_band;
     // fast FP64 kernels hand non-finite sums to the exact ones through the (by then consumed) guard list storage
     pd.guard = fast64 ? w->d_guard : nullptr; pd.guard_count = w->d_ints + INTS_GUARD64;
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) pd.resc_off[k] = w->resc_off[k];
@@ -776,7 +832,7 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     };
     cudaStream_t ks = st;
 
-    if (!fallback64) {
+    if (!fallback64 && !specfix) {
     CUDA_TRY(ctx, cudaEventRecord(w->ev[0], st));
     // ---- main pass over the planned tasks ---------------------------------------------------
     CUDA_TRY(ctx, fork());
@@ -851,13 +907,32 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
     }
     // ---- fast FP64 kernels only: non-finite sums re-run by the bit-exact FP64 kernel --------------
     // (launched by wl_finish when the counters say so: the common case pays nothing)
+    if (specfix) {
+        pf.mode = 3;
+        CUDA_TRY(ctx, fork());
+        for (int kh = 1; kh <= MAX_KH_SCALAR; ++kh) {
+            if (specfix[kh] == 0) continue;
+            CUDA_TRY(ctx, side_stream(&ks));
+            KernelF32 k = lookup_f32_l32_f0(kh);
+            pf.tasks = w->d_spec + w->spec_off[kh];
+            pf.ntasks_ptr = w->d_ints + INTS_SPEC + kh;
+            pf.counter = w->d_ints + INTS_COUNTER + SPEC_FIX_SLOT + kh;
+            if (!prepare((const void *)k, kh, std::min<int64_t>(specfix[kh], 4096), false, &grid, &smem)) { ctx->error = "cudaFuncSetAttribute failed"; return PHMM_ERR_CUDA; }
+            k<<<grid, WARPS_PER_BLOCK * 32, smem, ks>>>(pf);
+            CUDA_TRY(ctx, cudaGetLastError());
+            ++launches;
+        }
+        CUDA_TRY(ctx, join());
+        w->launches += launches;
+        return PHMM_OK;
+    }
     if (mode != 1 && fast64) {
         pd.guard = nullptr;
         counter_slot = MAX_STEP_LAUNCHES;  // queue heads reserved for this re-run: zeroed at the start of the step, never handed out by it
         CUDA_TRY(ctx, fork());
         for (int kh = 0; kh <= MAX_KH_SCALAR; ++kh) {
             if (fallback64[kh] == 0) continue;
-            if (counter_slot >= 64) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
+            if (counter_slot >= SPEC_FIX_SLOT) { ctx->error = "too many launches"; return PHMM_ERR_ARG; }
             CUDA_TRY(ctx, side_stream(&ks));
             KernelF64 k = kh ? lookup_f64(kh, false) : lookup_f64_long(false);
             pd.tasks = w->d_guard + w->resc_off[kh];
@@ -877,12 +952,23 @@ static int wl_launch(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, cudaEvent_t
 // After the stream set has drained: list counters and event times of the last launch.
 static int wl_finish(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, phmm_stats *stats)
 {
-    int32_t counts[49];
+    int32_t counts[INTS_LISTS];
     CUDA_TRY(ctx, cudaMemcpyAsync(counts, w->d_ints + INTS_RESC, sizeof counts, cudaMemcpyDeviceToHost, ss.main));
     CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
-    int64_t nguard = 0, n64 = 0;
-    const int64_t nres = counts[48];
-    for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nguard += counts[16 + k]; n64 += counts[32 + k]; }
+    int64_t nguard = 0, n64 = 0, nband = 0;
+    const int32_t *spec_counts = counts + (INTS_SPEC - INTS_RESC);
+    int64_t nres = (int64_t)counts[INTS_RESC_PAIRS - INTS_RESC] + spec_counts[MAX_KH_SCALAR + 1];
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nguard += counts[16 + k]; n64 += counts[32 + k]; nband += spec_counts[k]; }
+    w->last_spec_direct = spec_counts[MAX_KH_SCALAR + 2];
+    if (nband > 0) {
+        // FP64-first pairs whose rescaled sum fell inside the band around MIN_ACCEPTED: the bit-exact FP32 kernel decides
+        int rc = wl_launch(ctx, w, ss, nullptr, nullptr, spec_counts);
+        if (rc != PHMM_OK) return rc;
+        int32_t decided = 0;
+        CUDA_TRY(ctx, cudaMemcpyAsync(&decided, w->d_ints + INTS_RESC_PAIRS, sizeof decided, cudaMemcpyDeviceToHost, ss.main));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
+        nres += decided - counts[INTS_RESC_PAIRS - INTS_RESC];
+    }
     if (n64 > 0) {
         // fast FP64 kernels met non-finite sums (exotic gap-continuation penalties): bit-exact re-run
         int rc = wl_launch(ctx, w, ss, nullptr, counts + 32);
@@ -911,6 +997,9 @@ static int wl_finish(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, phmm_stats 
         stats->n_cells = w->n_cells;
         stats->n_rescued = nres;
         stats->n_guard = nguard;
+        stats->n_spec_pairs = w->spec_pairs;
+        stats->n_spec_cells = w->spec_cells;
+        stats->n_spec_direct = w->last_spec_direct;
         stats->n_launches = w->launches;
         stats->n_classes = (int32_t)w->classes.size();
         for (auto &cd : w->classes) stats->n_tasks += cd.ntasks;
@@ -994,6 +1083,7 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
                     s.ms_fp32, s.ms_fp64, s.ms_total, s.n_launches, (long long)s.n_tasks, wall_ms() - t_begin);
         agg.n_pairs += s.n_pairs; agg.n_cells += s.n_cells; agg.n_rescued += s.n_rescued;
         agg.n_guard += s.n_guard; agg.n_tasks += s.n_tasks; agg.h2d_bytes += s.h2d_bytes;
+        agg.n_spec_pairs += s.n_spec_pairs; agg.n_spec_cells += s.n_spec_cells; agg.n_spec_direct += s.n_spec_direct;
         agg.n_launches += s.n_launches; agg.n_classes = std::max(agg.n_classes, s.n_classes);
         agg.ms_fp32 += s.ms_fp32; agg.ms_fp64 += s.ms_fp64; agg.ms_total += s.ms_total;
         agg.d2h_bytes += w->n_pairs * (int64_t)sizeof(double);
@@ -1014,6 +1104,7 @@ extern "C" int phmm_compute_flat(phmm_ctx *ctx, const phmm_flat_batches *fb, dou
     PlanOptions popt = plan_options(ctx);
     popt.latency = plan_latency(*fb, popt);        // one decision for the whole call, not one per chunk
     popt.one_class = plan_one_class(*fb, popt);
+    popt.spec = plan_spec(*fb, popt);
     static const int n_planners_env = getenv("PHMM_PLANNERS") ? atoi(getenv("PHMM_PLANNERS")) : 0;
     const int n_planners = chunks.size() > 1
         ? std::max(1, std::min<int>({n_planners_env > 0 ? n_planners_env : 3, (int)chunks.size(),
@@ -1332,7 +1423,7 @@ static int submit_merged(phmm_ctx *ctx, const phmm_flat_batches &view, phmm_ctx:
     for (const phmm_ctx::Inflight &g : ctx->inflight)
         if (g.slot == f.slot) { int rc = phmm_wait(ctx, g.ticket, &ctx->retired_stats); if (rc != PHMM_OK) return rc; break; }
     PlanOptions popt = plan_options(ctx);
-    if (!prebuilt) { popt.latency = plan_latency(view, popt); popt.one_class = plan_one_class(view, popt); }
+    if (!prebuilt) { popt.latency = plan_latency(view, popt); popt.one_class = plan_one_class(view, popt); popt.spec = plan_spec(view, popt); }
     StreamSet &ss = ctx->ss[f.slot];
     int rc = wl_create(ctx, &view, &ctx->arena[f.slot], ctx->copy_in, &f.w, prebuilt, &popt);
     if (rc != PHMM_OK) return rc;
@@ -1476,12 +1567,14 @@ extern "C" int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s,
 
 // Plan-only summary (no device needed): used by the CPU test-suite to check the host logic.
 extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int seg_cols,
-                                 int64_t *info /* [8 + 4 * 16 + 2 * 16] */, uint8_t *pair_cover /* [n_pairs] or NULL */)
+                                 int64_t *info /* [8 + 4 * 16 + 2 * 16 + 2] */, uint8_t *pair_cover /* [n_pairs] or NULL */)
 {
     if (!fb || !info) return PHMM_ERR_ARG;
     PlanOptions o;
     o.precision = precision & 0xff;
     o.hp = (precision >> 8) & 1;          // plan for the fast FP32 (haplotype-pair) kernels
+    o.spec = (precision >> 9) & 1;        // ... with FP64-first reads (info[104] = their pairs, info[105] = their cells)
+    if ((precision >> 10) & 1) o.spec = -1;   // ... or decided from the input, as the library does (plan_spec)
     o.seg_cols = seg_cols;
     Plan P;
     std::string err;
@@ -1519,7 +1612,17 @@ extern "C" int phmm_plan_summary(const phmm_flat_batches *fb, int precision, int
         if (c < 16) { info[72 + 2 * c] = P.classes[c].cells; info[72 + 2 * c + 1] = tile; }
     }
     info[7] = tile_total;
+    if (o.spec) { info[104] = P.spec_pairs; info[105] = P.spec_cells; }
+    else { info[104] = 0; info[105] = 0; }
     if (pair_cover) {
+        for (int k = 0; k <= MAX_KH_SCALAR; ++k)
+            for (auto &t : P.spec_tasks[k]) {
+                int64_t cols = 0;
+                for (int j = 0; j < t.nh; ++j) cols += P.hap_len[t.hap0 + j] + SEP_COLS;
+                const ReadRec &rr = P.reads[t.read[0]];
+                if (cols != t.ncols || t.read[1] != SPEC_TASK || (rr.len + 1 + 31) / 32 != k) return PHMM_ERR_ARG;
+                for (int j = 0; j < t.nh; ++j) pair_cover[rr.out_base + t.out0 + j]++;
+            }
         // walk every task the way the kernel does and count how often each pair is produced
         for (auto &cp : P.classes)
             for (auto &t : cp.htasks)

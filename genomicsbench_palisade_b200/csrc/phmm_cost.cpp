@@ -41,24 +41,24 @@ namespace {
 const int K = 10;                                  // anchor length
 const uint32_t KMASK = (1u << (2 * K)) - 1;
 
-// Direct-address table of the k-mers of one haplotype; entries are validated by a stamp, so that moving on
-// to the next batch costs nothing.
+// Hashed table of the k-mers of one haplotype (64 K entries of stamp | position: 512 KB, so it stays in the
+// core's L2); a hit is verified against the haplotype's bases, entries are validated by a stamp, so that moving on
+// to the next batch costs nothing.  A later k-mer that hashes to the same entry replaces the earlier one.
+const int HBITS = 16;
 struct KmerIndex {
-    std::vector<int32_t> pos, stamp;
-    int32_t cur = 0;
-    KmerIndex() : pos(KMASK + 1, 0), stamp(KMASK + 1, 0) {}
+    std::vector<uint64_t> e;
+    uint32_t cur = 0;
+    KmerIndex() : e((size_t)1 << HBITS, 0) {}
 };
 
-inline int base2(uint8_t b)
-{
-    switch (b) {
-    case 'A': return 0;
-    case 'C': return 1;
-    case 'G': return 2;
-    case 'T': return 3;
-    default:  return -1;                           // N and everything else interrupts a k-mer
-    }
-}
+struct Base2Table {
+    int8_t t[256];
+    Base2Table() { memset(t, -1, sizeof t); t['A'] = 0; t['C'] = 1; t['G'] = 2; t['T'] = 3; }
+};
+const Base2Table g_base2;
+inline int base2(uint8_t b) { return g_base2.t[b]; }      // N and everything else (-1) interrupts a k-mer
+
+inline uint32_t slot_of(uint32_t key) { return (key * 2654435761u) >> (32 - HBITS); }
 
 void index_hap(KmerIndex &ix, const uint8_t *hap, int len)
 {
@@ -69,8 +69,50 @@ void index_hap(KmerIndex &ix, const uint8_t *hap, int len)
         const int c = base2(hap[i]);
         if (c < 0) { run = 0; continue; }
         key = ((key << 2) | (uint32_t)c) & KMASK;
-        if (++run >= K) { ix.pos[key] = i - K + 1; ix.stamp[key] = ix.cur; }
+        if (++run >= K) ix.e[slot_of(key)] = ((uint64_t)ix.cur << 32) | (uint32_t)(i - K + 1);
     }
+}
+
+// position in the haplotype of the k-mer that starts at `kmer` (K bases, key `key`), or -1
+inline int lookup(const KmerIndex &ix, uint32_t key, const uint8_t *hap, const uint8_t *kmer)
+{
+    const uint64_t v = ix.e[slot_of(key)];
+    if ((uint32_t)(v >> 32) != ix.cur) return -1;
+    const int pos = (int)(uint32_t)v;
+    return memcmp(hap + pos, kmer, K) == 0 ? pos : -1;
+}
+
+// Six k-mers spread over the read; four of them on (nearly) one diagonal of the haplotype: the read sits on it with few
+// mismatches and is nowhere near failing the FP32 pass.  This is what nine reads in ten look like, and it costs a
+// twentieth of anchored_score.
+bool sits_on_a_diagonal(const KmerIndex &ix, const uint8_t *hap, const uint8_t *rs, int rlen)
+{
+    const int NS = 6;
+    if (rlen < 4 * K) return false;
+    int d[NS], nd = 0;
+    for (int i = 0; i < NS; ++i) {
+        const int p = (int)((int64_t)i * (rlen - K) / (NS - 1));
+        uint32_t key = 0;
+        bool ok = true;
+        for (int j = 0; j < K && ok; ++j) {
+            const int c = base2(rs[p + j]);
+            ok = c >= 0;
+            key = (key << 2) | (uint32_t)(c & 3);
+        }
+        if (!ok) continue;
+        const int pos = lookup(ix, key & KMASK, hap, rs + p);
+        if (pos >= 0) d[nd++] = pos - p;
+        if (i == 3 && nd == 4 && d[1] >= d[0] - 48 && d[1] <= d[0] + 48 && d[2] >= d[0] - 48 && d[2] <= d[0] + 48 &&
+            d[3] >= d[0] - 48 && d[3] <= d[0] + 48)
+            return true;                                   // the common case: the first four agree
+    }
+    // (diagonals within a few dozen columns of each other: an indel between two anchors shifts the later ones)
+    for (int i = 0; i + 3 < nd; ++i) {
+        int same = 1;
+        for (int j = i + 1; j < nd; ++j) same += (d[j] >= d[i] - 48 && d[j] <= d[i] + 48);
+        if (same >= 4) return true;
+    }
+    return false;
 }
 
 struct LogTables {
@@ -100,8 +142,9 @@ float anchored_score(const KmerIndex &ix, const LogTables &lt, const uint8_t *ha
         if (c < 0) { run = 0; continue; }
         key = ((key << 2) | (uint32_t)c) & KMASK;
         if (++run < K || ((r + 1) & 1)) continue;                       // every second k-mer
-        if (ix.stamp[key] != ix.cur) continue;
-        const int d = ix.pos[key] - (r - K + 1);
+        const int pos = lookup(ix, key, hap, rs + (r - K + 1));
+        if (pos < 0) continue;
+        const int d = pos - (r - K + 1);
         int j = 0;
         while (j < nv && votes[j].d != d) ++j;
         if (j < nv) ++votes[j].n;
@@ -110,6 +153,14 @@ float anchored_score(const KmerIndex &ix, const LogTables &lt, const uint8_t *ha
     if (nv > 3) {
         std::partial_sort(votes, votes + 3, votes + nv, [](const Vote &a, const Vote &b) { return a.n > b.n; });
         nv = 3;
+    }
+    // a diagonal that a single k-mer voted for is a chance hit (an unrelated read collects one or two of those):
+    // scoring the read along it costs a pass over the read per diagonal and changes nothing
+    {
+        int kept = 0;
+        for (int j = 0; j < nv; ++j)
+            if (votes[j].n >= 2) votes[kept++] = votes[j];
+        nv = kept;
     }
     float s = 0.0f;
     if (nv == 0) {
@@ -134,16 +185,77 @@ float anchored_score(const KmerIndex &ix, const LogTables &lt, const uint8_t *ha
 
 }  // namespace
 
+bool spec_enabled()
+{
+    static const bool on = !(getenv("PHMM_SPEC64") && atoi(getenv("PHMM_SPEC64")) == 0);
+    return on;
+}
+
+// Whether a call is planned with FP64-first reads (PlanOptions::spec = -1: from the input).  The predictor costs the
+// planner 0.12 us per read that sits on a diagonal and ~2 us per read that does not -- more than the rest of the plan
+// (0.085 us per read) -- so it runs only where it can pay: when a read is at least ~0.7 us of device work (2.5e6
+// cells: C1-shaped input, whose end-to-end rate is bound by planning, stays as it is) and when a sample of the reads
+// (about 600 of them, spread over every third batch) has at least 1 % of them failing the FP32 pass by a factor of ten.
+// Decided once per host-buffer call, like the latency plan: a pair's result does not depend on the cut into chunks.
+int plan_spec(const phmm_flat_batches &fb, const PlanOptions &opt)
+{
+    if (opt.spec >= 0) return opt.spec;
+    if (!opt.hp || opt.precision != 0 || opt.latency == 1 || opt.force_kh > 0 || fb.n_reads <= 0 || fb.n_batches <= 0) return 0;
+    if (!fb.batch_num_reads || !fb.batch_num_haps || !fb.read_len || !fb.hap_len || !fb.read_off || !fb.hap_off) return 0;
+    double cells = 0;
+    {
+        int64_t r0 = 0, h0 = 0;
+        for (int64_t b = 0; b < fb.n_batches; ++b) {
+            const int nr = fb.batch_num_reads[b], nh = fb.batch_num_haps[b];
+            if (nr < 0 || nh < 0 || r0 + nr > fb.n_reads || h0 + nh > fb.n_haps) return 0;
+            double sr = 0, sh = 0;
+            for (int k = 0; k < nr; ++k) sr += fb.read_len[r0 + k];
+            for (int k = 0; k < nh; ++k) sh += fb.hap_len[h0 + k];
+            cells += sr * sh;
+            r0 += nr; h0 += nh;
+        }
+    }
+    if (cells < 2.5e6 * (double)fb.n_reads) return 0;
+    static const LogTables lt;
+    thread_local KmerIndex ix;
+    // about 600 reads, spread over the batches
+    const int64_t bstride = fb.n_batches >= 12 ? 3 : 1;
+    const int rstride = (int)std::max<int64_t>(4, fb.n_reads / (bstride * 600));
+    int64_t seen = 0, sure = 0, r0 = 0, h0 = 0;
+    for (int64_t b = 0; b < fb.n_batches; ++b) {
+        const int nr = fb.batch_num_reads[b], nh = fb.batch_num_haps[b];
+        if (b % bstride == 0 && nr > 0 && nh > 0 && fb.hap_len[h0] > 0) {
+            const uint8_t *hap = fb.hap + fb.hap_off[h0];
+            const int hlen = fb.hap_len[h0];
+            index_hap(ix, hap, hlen);
+            for (int k = (int)(b % rstride); k < nr; k += rstride) {
+                const int len = fb.read_len[r0 + k];
+                if (len <= 0) return 0;
+                const int64_t ro = fb.read_off[r0 + k];
+                ++seen;
+                if (sits_on_a_diagonal(ix, hap, fb.rs + ro, len)) continue;
+                const float s = anchored_score(ix, lt, hap, hlen, fb.rs + ro, fb.q + ro, fb.c + ro, len);
+                // batch_costs' test with the 1 / haplen prior left out: stricter than for any haplotype
+                if (s + 36.1236 + 28.0 < -1.0) ++sure;
+            }
+        }
+        r0 += nr; h0 += nh;
+    }
+    return seen > 0 && sure * 100 >= seen ? 1 : 0;
+}
+
 int batch_costs(const phmm_flat_batches &fb, int fast, int precision, const CostModel &m, int64_t *cost,
                 uint8_t *read_rescued)
 {
     if (fb.n_batches < 0 || (fb.n_batches && (!fb.batch_num_reads || !fb.batch_num_haps || !cost))) return PHMM_ERR_ARG;
     static const LogTables lt;
     thread_local KmerIndex ix;
+    std::vector<double> log_hl;
     PlanOptions opt;
     opt.precision = precision;
     opt.hp = fast ? 1 : 0;
     opt.latency = 0;
+    const bool spec = fast && precision == 0 && spec_enabled();
     double w_of_len[512];
     for (double &v : w_of_len) v = -1.0;
     // tile weight of a read: device time per haplotype column, in units of one FP32 row step of the fast kernels
@@ -178,23 +290,37 @@ int batch_costs(const phmm_flat_batches &fb, int fast, int precision, const Cost
         for (int k = 0; k < nh; ++k) cols += fb.hap_len[h0 + k] + SEP_COLS;
         double c32 = 0, c64 = 0;
         const bool predict = precision == 0 && nh > 0 && nr > 0 && fb.hap_len[h0] > 0;
-        if (predict) index_hap(ix, fb.hap + fb.hap_off[h0], fb.hap_len[h0]);
+        if (predict) {
+            index_hap(ix, fb.hap + fb.hap_off[h0], fb.hap_len[h0]);
+            log_hl.resize((size_t)nh);
+            for (int j = 0; j < nh; ++j) log_hl[(size_t)j] = std::log10((double)std::max(fb.hap_len[h0 + j], 1));
+        }
         for (int k = 0; k < nr; ++k) {
             const int len = fb.read_len[r0 + k];
             if (len <= 0) return PHMM_ERR_EMPTY_SEQ;
             c32 += weight32(len);
             if (!predict) continue;
             const int64_t ro = fb.read_off[r0 + k];
+            if (sits_on_a_diagonal(ix, fb.hap + fb.hap_off[h0], fb.rs + ro, len)) {
+                if (read_rescued) read_rescued[r0 + k] = 0;
+                continue;
+            }
             const float s = anchored_score(ix, lt, fb.hap + fb.hap_off[h0], fb.hap_len[h0], fb.rs + ro, fb.q + ro, fb.c + ro, len);
             // FP32 sum = likelihood * 2^120 with prior 1 / haplen; rescued when below MIN_ACCEPTED = 1e-28
             double rc = 0;
-            int n_resc = 0;
+            int n_resc = 0, n_sure = 0;
             for (int j = 0; j < nh; ++j) {
                 const int hl = fb.hap_len[h0 + j];
-                if (s - std::log10((double)hl) + 36.1236 < -28.0) { rc += hl + SEP_COLS + 32; ++n_resc; }
+                const double margin = s - log_hl[(size_t)j] + 36.1236 + 28.0;
+                if (margin < 0) { rc += hl + SEP_COLS + 32; ++n_resc; }
+                if (margin < -1.0) ++n_sure;
             }
             c64 += rc * weight64(len);
-            if (read_rescued) read_rescued[r0 + k] = (uint8_t)(2 * n_resc >= nh ? 1 : 0);
+            // bit 0: most pairs of the read predicted rescued; bit 1: all of them, by at least a factor of ten -- such a
+            // read is planned FP64-first (PlanOptions::spec) and costs no FP32 pass
+            const bool sure = n_sure == nh && len + 1 <= 32 * MAX_KH_SCALAR;
+            if (sure && spec) c32 -= weight32(len);
+            if (read_rescued) read_rescued[r0 + k] = (uint8_t)((2 * n_resc >= nh ? 1 : 0) | (sure ? 2 : 0));
         }
         if (!predict && read_rescued) memset(read_rescued + r0, 0, (size_t)nr);
         cost[b] = (int64_t)std::llround(c32 * cols + c64);

@@ -238,6 +238,7 @@ int compute_regions_pipelined(phmm_gatk *g, const phmm_gatk_region *regions, int
                 phmm::PlanOptions popt = popt0;
                 popt.latency = phmm::plan_latency(b.view, popt);
                 popt.one_class = phmm::plan_one_class(b.view, popt);
+                popt.spec = phmm::plan_spec(b.view, popt);
                 rc = phmm::build_plan(b.view, popt, &G.plan, &G.err);
             }
             std::lock_guard<std::mutex> lk(mu);

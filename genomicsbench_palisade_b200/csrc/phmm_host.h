@@ -33,6 +33,8 @@ struct PlanOptions {
     int force_kh = 0, force_lanes = 0;   // debugging / benchmarking: pin the kernel class
     int hp = 0;               // 1 = plan haplotype-pair tasks (fast FP32 kernels) for single-pass reads
     int latency = -1;         // 1 = plan for the latency of a small call (32 lanes per read, one haplotype per run); -1 = decide from the size
+    int spec = 0;             // -1 = decide from the input (plan_spec, once per call); 1 = FP64-first: reads predicted to fail the FP32 pass against their whole batch (phmm_cost.cpp) skip it;
+                              // their tasks are laid into the rescue lists by the planner (fast FP32 kernels, precision 0, throughput plans)
     int one_class = -1;       // latency plans whose tasks fit the device in one wave: > 0 = every read in the 32-lane class of this
                               // height, all rescue / guard work in that scalar class; 0 = classes by read length; -1 = decide from the input
 };
@@ -67,6 +69,10 @@ struct Plan {
     std::vector<Segment> segments;
     int64_t pool_len = 0;                // sum of segment lengths
     int64_t resc_cap[MAX_KH_SCALAR + 1]; // pairs whose read falls in each scalar class
+    // FP64-first tasks per scalar class (Task::read[1] == SPEC_TASK): the head of that class's rescue list
+    std::vector<Task> spec_tasks[MAX_KH_SCALAR + 1];
+    int64_t spec_cap[MAX_KH_SCALAR + 1]; // pairs of FP64-first reads per class (capacity of the band list)
+    int64_t spec_pairs = 0, spec_cells = 0;
     int resc_force = 0;                  // > 0: one-wave call, all rescue / guard work in this scalar class (KernelParams::resc_force)
     int max_rslen = 0, max_haplen = 0;
     int long_max_cols = 0;               // longest run handed to a multi-pass kernel (0 = none)
@@ -101,6 +107,9 @@ CostModel default_cost_model();
 // most pairs of the read to be re-run in FP64.
 int batch_costs(const phmm_flat_batches &fb, int fast, int precision, const CostModel &m, int64_t *cost,
                 uint8_t *read_rescued);
+// FP64-first planning on (default) unless PHMM_SPEC64=0
+bool spec_enabled();
+int plan_spec(const phmm_flat_batches &fb, const PlanOptions &opt);      // opt.latency resolved; once per call
 
 // ---- kernels (phmm_inst_*.cu, phmm_microbench.cu) -------------------------------------------
 typedef void (*KernelF32)(const KernelParams<float>);

@@ -203,6 +203,12 @@ __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float 
         redo = !(res <= 3.402823466e+38f) ||
                (P.mode == 0 && res >= MIN_ACCEPTED_F * (1.0f - rel) && res < MIN_ACCEPTED_F * (1.0f + rel));
     }
+    if (P.mode == 3 && res < MIN_ACCEPTED_F) {
+        // deciding an FP64-first pair whose rescaled FP64 sum fell inside the band: the FP32 pass fails, the FP64
+        // result the pair already holds stands (KernelParams::spec_list)
+        atomicAdd(P.resc_pairs, 1);
+        return;
+    }
     if (redo || (P.mode == 0 && res < MIN_ACCEPTED_F)) {
         // :73-75 -- below MIN_ACCEPTED the pair is re-run in FP64 (by the FP64 kernel of the
         // read's class).
@@ -232,8 +238,43 @@ __device__ __forceinline__ void emit_result(const KernelParams<float> &P, float 
 template <bool FAST>
 __device__ __forceinline__ void emit_result(const KernelParams<double> &P, double res, int64_t oidx,
                                             int64_t hap_stream_off, int hap_len, int hap_idx,
-                                            int out_rel, int rid, int rslen)
+                                            int out_rel, int rid, int rslen, bool spec = false)
 {
+    if (spec && P.mode == 0) {
+        // FP64-first pair: what would the FP32 pass have summed?  The same recurrence from 2^120 instead of 2^1020;
+        // its rounding error is <= ~5 (R + H) ulp relative on an all-positive recurrence, underflow only lowers it by
+        // < 1e-33 absolute.  Band = 16 x that bound, never less than spec_band (2^-6).
+        const double est = res * 0x1p-900;
+        const double rel = fmax((double)P.spec_band, (double)(rslen + hap_len) * 4.768e-6);
+        const double thr = (double)MIN_ACCEPTED_F;
+        if (!(est < thr * (1.0 - rel))) {
+            if (est >= thr * (1.0 + rel) && est <= 3.0e38) {
+                // not rescued after all: the FP32 path's result (:78), from the rescaled sum
+                const float s32 = (float)est;
+                P.raw32[oidx] = s32;
+                P.out[oidx] = (double)__fsub_rn(log10f(s32), P.log10_init32);
+                P.rescued[oidx] = 0;
+                atomicAdd(P.spec_count + MAX_KH_SCALAR + 2, 1);
+                return;
+            }
+            // inside the band (or not finite): the FP64 result below stands unless the bit-exact FP32 kernel, which
+            // runs on spec_list afterwards, says the pair passes
+            Task nt;
+            nt.stream_off = hap_stream_off;
+            nt.ncols = hap_len + SEP_COLS;
+            nt.hap0 = hap_idx;
+            nt.out0 = out_rel;
+            nt.read[0] = rid; nt.read[1] = -1; nt.read[2] = -1; nt.read[3] = -1;
+            nt.nh = 1;
+            const int ci = list_class(P, rslen);
+            const int k = atomicAdd(&P.spec_count[ci], 1);
+            P.spec_list[P.spec_off[ci] + k] = nt;
+            if (!(res <= 1.7976931348623157e+308)) { P.rescued[oidx] = 1; P.out[oidx] = res; return; }
+        } else {
+            atomicAdd(P.spec_count + MAX_KH_SCALAR + 1, 1);
+        }
+        P.raw32[oidx] = (float)est;
+    }
     // Fast FP64 kernel (scaled recurrence): X / sigma can overflow for exotic gap-continuation
     // penalties; a non-finite sum is re-run by the bit-exact FP64 kernel of the read's class.
     if (FAST && P.guard && !(res <= 1.7976931348623157e+308)) {
@@ -253,6 +294,19 @@ __device__ __forceinline__ void emit_result(const KernelParams<double> &P, doubl
     P.raw64[oidx] = res;
     P.out[oidx] = __dsub_rn(log10(res), P.log10_init);
     P.rescued[oidx] = (P.mode == 0) ? 1 : 0;
+}
+
+template <bool FAST>
+__device__ __forceinline__ void emit_result_spec(const KernelParams<double> &P, double res, int64_t oidx, int64_t hap_stream_off,
+                                                 int hap_len, int hap_idx, int out_rel, int rid, int rslen, bool spec)
+{
+    emit_result<FAST>(P, res, oidx, hap_stream_off, hap_len, hap_idx, out_rel, rid, rslen, spec);
+}
+template <bool FAST>
+__device__ __forceinline__ void emit_result_spec(const KernelParams<float> &P, float res, int64_t oidx, int64_t hap_stream_off,
+                                                 int hap_len, int hap_idx, int out_rel, int rid, int rslen, bool)
+{
+    emit_result<FAST>(P, res, oidx, hap_stream_off, hap_len, hap_idx, out_rel, rid, rslen);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -603,8 +657,10 @@ phmm_forward_kernel(const KernelParams<T> P)
                                 if (rid[c] >= 0) {
                                     const T res = SCALED ? O::get(sumM, c) + O::get(sumX, c) * O::get(fin, c)
                                                          : S::add(O::get(sumM, c), O::get(sumX, c));   // :342
-                                    emit_result<FAST>(P, res, out_base[c] + out0 + jh, stream_off + hapstart, hl,
-                                                      hap0 + jh, out0 + jh, rid[c], R[c]);
+                                    if (VL == 1) emit_result_spec<FAST>(P, res, out_base[c] + out0 + jh, stream_off + hapstart, hl,
+                                                                        hap0 + jh, out0 + jh, rid[c], R[c], tk->read[1] == SPEC_TASK);
+                                    else emit_result<FAST>(P, res, out_base[c] + out0 + jh, stream_off + hapstart, hl,
+                                                           hap0 + jh, out0 + jh, rid[c], R[c]);
                                 }
                             hapstart += hl + SEP_COLS;
                         }

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 
 #include "phmm_host.h"
 
@@ -138,6 +139,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
         P.max_rslen = std::max(P.max_rslen, len);
     }
     if (opt.one_class < 0) opt.one_class = plan_one_class(fb, opt);
+    if (opt.spec < 0) opt.spec = plan_spec(fb, opt);
     if (opt.one_class > 0 && opt.force_kh <= 0) {
         opt.force_kh = opt.one_class;
         opt.force_lanes = 32;
@@ -270,6 +272,55 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
     }
     const size_t ncls = P.classes.size();
 
+    // ---- FP64-first reads (PlanOptions::spec) -----------------------------------------------------------
+    // A read that the k-mer predictor (phmm_cost.cpp) expects to fail the FP32 pass against every haplotype of its
+    // batch, by a factor of ten at least, skips that pass: its tasks (runs of up to 4 haplotypes / 2048 columns, as
+    // the fast kernels hand rescued pairs over) are laid into the rescue lists here, and the FP64 kernel checks on the
+    // rescaled sum what the FP32 pass would have decided (phmm_kernels.cuh: emit_result).
+    const bool spec = opt.spec > 0 && opt.hp && opt.precision == 0 && opt.latency != 1 && opt.force_kh <= 0 && fb.n_reads > 0;
+    std::vector<uint8_t> pred;
+    for (int k = 0; k <= MAX_KH_SCALAR; ++k) P.spec_cap[k] = 0;
+    if (spec) {
+        pred.assign((size_t)fb.n_reads, 0);
+        std::vector<int64_t> cost_unused((size_t)std::max<int64_t>(fb.n_batches, 1));
+        // the prediction is the longest part of planning a large chunk (2 us per read that sits on no diagonal), and
+        // the chunk's upload waits for its plan: slices of batches on up to four threads
+        const unsigned hw = std::thread::hardware_concurrency();
+        const int nthr = (fb.n_reads >= 4000 && fb.n_batches >= 4) ? (hw >= 16 ? 4 : hw >= 8 ? 2 : 1) : 1;
+        std::vector<int64_t> cut_b(1, 0), cut_r(1, 0), cut_h(1, 0);
+        {
+            int64_t r = 0, h = 0;
+            for (int64_t b = 0; b < fb.n_batches; ++b) {
+                r += fb.batch_num_reads[b];
+                h += fb.batch_num_haps[b];
+                if (b + 1 == fb.n_batches || r >= (int64_t)cut_b.size() * fb.n_reads / nthr) {
+                    cut_b.push_back(b + 1); cut_r.push_back(r); cut_h.push_back(h);
+                }
+            }
+        }
+        std::vector<int> rcs(cut_b.size() - 1, PHMM_OK);
+        auto slice = [&](size_t j) {
+            phmm_flat_batches v = fb;
+            v.n_batches = cut_b[j + 1] - cut_b[j];
+            v.batch_num_reads = fb.batch_num_reads + cut_b[j];
+            v.batch_num_haps = fb.batch_num_haps + cut_b[j];
+            v.n_reads = cut_r[j + 1] - cut_r[j];
+            v.read_len = fb.read_len + cut_r[j];
+            v.read_off = fb.read_off + cut_r[j];
+            v.n_haps = cut_h[j + 1] - cut_h[j];
+            v.hap_len = fb.hap_len + cut_h[j];
+            v.hap_off = fb.hap_off + cut_h[j];
+            rcs[j] = batch_costs(v, 1, 0, default_cost_model(), cost_unused.data() + cut_b[j], pred.data() + cut_r[j]);
+        };
+        std::vector<std::thread> helpers;
+        for (size_t j = 1; j + 1 < cut_b.size(); ++j) helpers.emplace_back(slice, j);
+        slice(0);
+        for (std::thread &t : helpers) t.join();
+        for (int rc1 : rcs) if (rc1 != PHMM_OK) { pred.assign((size_t)fb.n_reads, 0); break; }
+    }
+    struct SpecRun { int k0, k1; int32_t cols; };
+    std::vector<SpecRun> spec_runs;
+
     // ---- per batch: reads by class --------------------------------------------------------------
     // rl[b * ncls + c] = reads of batch b handled by class c.  A class's leftover reads (fewer
     // than one full task) move up to the next larger class of the batch, where they fill slots
@@ -304,6 +355,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
             for (int k = 0; k < bnh; ++k) sum_h += fb.hap_len[h0 + k];
             binfo[b] = BatchInfo{r0, h0, out0, sum_h + (int64_t)bnh * SEP_COLS};
             for (auto &v : scratch) v.clear();
+            spec_runs.clear();
             std::vector<int32_t> *by_class = scratch.data();
             for (int k = 0; k < bnr; ++k) {
                 const int64_t r = r0 + k;
@@ -312,9 +364,38 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
                 rr.len = fb.read_len[r];
                 rr.batch = (int32_t)b;
                 rr.out_base = out0 + (int64_t)k * bnh;
-                by_class[read_class[r]].push_back((int32_t)r);
                 P.n_cells += (int64_t)rr.len * sum_h;
-                P.resc_cap[P.resc_force > 0 ? P.resc_force : scalar_class_of(rr.len)] += bnh;
+                const int sc = P.resc_force > 0 ? P.resc_force : scalar_class_of(rr.len);
+                P.resc_cap[sc] += bnh;
+                if (spec && (pred[(size_t)r] & 2) && sc > 0 && bnh > 0) {
+                    if (spec_runs.empty())
+                        for (int j = 0; j < bnh;) {
+                            int j1 = j;
+                            int32_t cols = 0;
+                            while (j1 < bnh && (j1 == j || (j1 - j < 4 && cols + fb.hap_len[h0 + j1] + SEP_COLS <= 2048))) {
+                                cols += fb.hap_len[h0 + j1] + SEP_COLS;
+                                ++j1;
+                            }
+                            spec_runs.push_back(SpecRun{j, j1, cols});
+                            j = j1;
+                        }
+                    for (const SpecRun &sr : spec_runs) {
+                        Task t;
+                        t.stream_off = hap_col[h0 + sr.k0];
+                        t.ncols = sr.cols;
+                        t.hap0 = (int32_t)(h0 + sr.k0);
+                        t.out0 = sr.k0;
+                        t.read[0] = (int32_t)r; t.read[1] = SPEC_TASK; t.read[2] = -1; t.read[3] = -1;
+                        t.nh = sr.k1 - sr.k0;
+                        P.spec_tasks[sc].push_back(t);
+                    }
+                    P.resc_cap[sc] += (int64_t)spec_runs.size();      // the list also holds what the kernels append
+                    P.spec_cap[sc] += bnh;
+                    P.spec_pairs += bnh;
+                    P.spec_cells += (int64_t)rr.len * sum_h;
+                    continue;
+                }
+                by_class[read_class[r]].push_back((int32_t)r);
             }
             int prev = -1;
             for (size_t oi = 0; oi < ncls; ++oi) {

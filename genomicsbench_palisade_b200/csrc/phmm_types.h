@@ -50,6 +50,7 @@ struct HapSrc {
 // f32x2 half): read[2 * group + half]; FP64 kernels one: read[group].  The FP32 kernels also emit
 // these (one read, one haplotype) as FP64-rescue / guard-band work.
 static const int MAX_GROUP = 4;
+static const int32_t SPEC_TASK = -2;          // Task::read[1] of an FP64-first task (FP64 kernels read read[0] only)
 struct Task {
     int64_t stream_off;  // first column of the run in the haplotype stream
     int32_t ncols;       // columns incl. SEP_COLS separator columns after every haplotype
@@ -141,6 +142,18 @@ struct KernelParams {
                                          // Plan::resc_force); 0: by read length
     Task *guard;                         // guard-band list (fast kernel only)
     int32_t *guard_count;
+    // FP64-first ("speculative") tasks, FP64 kernels only: a read the planner predicts to fail the FP32 pass against
+    // every haplotype of its batch skips that pass; its tasks (read[1] == SPEC_TASK) sit in the rescue lists from the
+    // start.  The FP64 sum, rescaled to the FP32 recurrence's 2^120, tells what the FP32 pass would have decided:
+    // clearly below MIN_ACCEPTED -> rescued, as predicted; clearly above -> the FP32 result is that value to ~1e-5,
+    // finalised here in float; within the band around the threshold -> spec_list, where the bit-exact FP32 kernel
+    // decides (mode 3).  See phmm_kernels.cuh: emit_result.
+    Task *spec_list;
+    int32_t *spec_count;                 // [MAX_KH_SCALAR + 1] tasks per class in spec_list, then [+ 9] pairs rescued as predicted,
+                                         // [+ 10] pairs finalised in float
+    int32_t spec_off[MAX_KH_SCALAR + 1];
+    float log10_init32;                  // log10f(2^120)
+    float spec_band;                     // > 0: relative half-width of the band is max(this, (R + H) * 4.768e-6)
     T *scratch;                          // multi-pass kernels: per-warp boundary rows
     int64_t scratch_stride;              // elements of T per warp (2 buffers x 3 arrays x columns)
 };

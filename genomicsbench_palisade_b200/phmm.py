@@ -43,7 +43,8 @@ class CStats(C.Structure):
                 ("n_rescued_cells", C.c_int64), ("n_guard", C.c_int64), ("n_tasks", C.c_int64),
                 ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64), ("n_launches", C.c_int32),
                 ("n_classes", C.c_int32), ("ms_fp32", C.c_float), ("ms_fp64", C.c_float),
-                ("ms_total", C.c_float), ("ms_h2d", C.c_float), ("ms_d2h", C.c_float)]
+                ("ms_total", C.c_float), ("ms_h2d", C.c_float), ("ms_d2h", C.c_float),
+                ("n_spec_pairs", C.c_int64), ("n_spec_cells", C.c_int64), ("n_spec_direct", C.c_int64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -317,12 +318,16 @@ def batch_costs(fb: FlatBatches, fast: bool = True, precision: int = BOTH, predi
     return (cost, pred[:len(fb.read_len)]) if predicted else cost
 
 
-def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True, fast=False):
+def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True, fast=False, fp64_first=False):
+    """fp64_first (with fast): plan as the library does by default for the fast kernels -- reads predicted to fail the
+    FP32 pass against their whole batch get FP64-first tasks instead of a place in an FP32 class; "auto" = only when the
+    library's per-call rule (plan_spec: work per read, share of such reads in a sample) says so."""
     lib = load_library()
     keep = _Keep(fb)
-    info = np.zeros(8 + 64 + 32, np.int64)
+    info = np.zeros(8 + 64 + 32 + 2, np.int64)
     cov = np.zeros(max(1, fb.n_pairs), np.uint8) if cover else None
-    rc = lib.phmm_plan_summary(C.byref(keep.c), C.c_int(precision | (0x100 if fast else 0)), C.c_int(seg_cols),
+    rc = lib.phmm_plan_summary(C.byref(keep.c), C.c_int(precision | (0x100 if fast else 0) | (0x400 if fp64_first == "auto" else 0x200 if fp64_first else 0)),
+                               C.c_int(seg_cols),
                                _ptr(info), _ptr(cov) if cover else None)
     if rc:
         raise PhmmError(rc, "phmm_plan_summary")
@@ -332,7 +337,8 @@ def plan_summary(fb: FlatBatches, precision=0, seg_cols=0, cover=True, fast=Fals
     return {"pairs": int(info[0]), "cells": int(info[1]), "n_classes": ncls, "stream_bytes": int(info[3]),
             "max_rslen": int(info[4]), "max_haplen": int(info[5]), "tasks": int(info[6]),
             "tile_cells": int(info[7]), "class_cells": fill,
-            "classes": classes, "cover": cov[:fb.n_pairs] if cover else None}
+            "classes": classes, "cover": cov[:fb.n_pairs] if cover else None,
+            "fp64_first_pairs": int(info[104]), "fp64_first_cells": int(info[105])}
 
 
 def get_tables():

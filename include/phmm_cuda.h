@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define PHMM_ABI_VERSION 4
+#define PHMM_ABI_VERSION 5
 
 /* ---- status codes (the reference defines none: it asserts / exit(0)s) ---- */
 #define PHMM_OK              0
@@ -139,6 +139,10 @@ typedef struct {
     float   ms_fp64;            /* ... of the FP64 rescue kernels                              */
     float   ms_total;           /* first launch to last kernel end                            */
     float   ms_h2d, ms_d2h;     /* host-buffer entry points only                               */
+    /* ABI 5.  FP64-first reads (fast FP32 kernels, both precisions): reads the planner predicts to fail the FP32
+     * pass against their whole batch skip it; the FP64 kernel checks on the rescaled sum what that pass would have
+     * decided.  n_spec_direct: pairs of such reads that pass after all (finalised from the FP64 sum in float). */
+    int64_t n_spec_pairs, n_spec_cells, n_spec_direct;
 } phmm_stats;
 
 /* ---- lifetime ------------------------------------------------------------------------------
@@ -325,7 +329,8 @@ int phmm_microbench(phmm_ctx *ctx, int which, double *lane_ops_per_s, float *ms)
  * haplotype-pair tasks, two runs of haplotypes per read).  info[0..6] = pairs, cells, classes, stream bytes,
  * max rslen, max haplen, tasks, tile cells (what the FP32 kernels compute: kh x lanes rows per read, separator
  * columns included); info[8 + 4c ..] = {kh, lanes, vl, tasks} and info[72 + 2c ..] = {cells, tile cells} of class c
- * (c < 16; info holds 104 values);
+ * (c < 16); precision | 0x200 adds FP64-first reads to that plan (| 0x400: only if the library would, by its per-call rule): info[104] = their pairs, info[105] = their cells (info
+ * holds 106 values);
  * pair_cover[p] is incremented once for every task that produces pair p. */
 int phmm_get_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d, float *consts_f,
                     double *consts_d);

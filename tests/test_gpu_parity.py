@@ -532,6 +532,55 @@ def test_gatk_large_call_is_staged_in_groups_under_the_kernels():
     assert "gatk pipelined call" in pr.stderr, "the large call did not take the pipelined path"
 
 
+_FP64_FIRST = r"""
+import sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from genomicsbench_palisade_b200 import phmm, synth
+fb = synth.generic(synth.SEED0 + 81, 40, (20, 40), (40, 64), (100, 250), (150, 473), foreign_frac=0.2)
+eng = phmm.PairHMM(fast=True, fast64=True)
+w = eng.workload(fb)
+st = w.run()
+st2 = w.run()                                   # the lists' heads are restored for every run
+out, raw32, raw64, resc = w.results(raw=True)
+w.close()
+flat = eng.compute(fb)                          # and the chunked host-buffer call returns the same
+eng.close()
+assert st["n_rescued"] == st2["n_rescued"] and np.array_equal(flat.view(np.uint64), out.view(np.uint64))
+np.savez(sys.argv[2], out=out, resc=resc, raw64=raw64, n_rescued=st["n_rescued"], spec=st["n_spec_pairs"],
+         direct=st["n_spec_direct"], launches=st["n_launches"])
+"""
+
+
+def test_fp64_first_reads_keep_results_and_rescue_set(tmp_path):
+    # Reads predicted to fail the FP32 pass against their whole batch run FP64 first (PlanOptions::spec).  Default,
+    # every such pair forced through the band list and the bit-exact FP32 decision (PHMM_SPEC_BAND huge), and the feature
+    # off must agree: same rescue set as the oracle, rescued pairs bit for bit, the rest within the FP32 bar.
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    fb = synth.generic(synth.SEED0 + 81, 40, (20, 40), (40, 64), (100, 250), (150, 473), foreign_frac=0.2)
+    ref = oracle.run_port(fb)
+    r = ref.rescued.astype(bool)
+    res = {}
+    for name, env in (("default", {}), ("band", {"PHMM_SPEC_BAND": "1e9"}), ("off", {"PHMM_SPEC64": "0"})):
+        path = str(tmp_path / (name + ".npz"))
+        pr = subprocess.run([sys.executable, "-c", _FP64_FIRST, ROOT, path], capture_output=True, text=True, timeout=600,
+                            env=dict(os.environ, **env))
+        assert pr.returncode == 0, pr.stderr[-3000:]
+        z = res[name] = np.load(path)
+        assert np.array_equal(z["resc"], ref.rescued), name
+        assert int(z["n_rescued"]) == int(r.sum()), name
+        assert same_or_close(z["out"][~r], ref.out[~r], RTOL_FP32) and same_or_close(z["out"][r], ref.out[r], RTOL_FP64), name
+    assert int(res["default"]["spec"]) > 0.1 * fb.n_pairs and int(res["band"]["spec"]) == int(res["default"]["spec"])
+    assert int(res["off"]["spec"]) == 0
+    assert int(res["band"]["launches"]) > int(res["default"]["launches"])          # the decision pass ran
+    for name in ("band", "off"):
+        assert np.array_equal(res[name]["out"][r].view(np.uint64), res["default"]["out"][r].view(np.uint64)), name
+        assert np.array_equal(res[name]["raw64"][r].view(np.uint64), res["default"]["raw64"][r].view(np.uint64)), name
+
+
 def test_driver_cli_with_binary_cache(tmp_path):
     # the rewritten driver: text input, then the same input mapped from its binary cache
     import os

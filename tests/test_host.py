@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     # the reference's own C++-linkage symbols (IntelPairHmmCSource.cpp:29,61,89,103; pairhmm_common.cc:3)
     for name in phmm.LEGACY_EXPORTS:
         assert hasattr(lib, name), name
-    assert lib.phmm_abi_version() == 4
+    assert lib.phmm_abi_version() == 5
 
 
 def test_no_cpu_fallback_without_a_device():
@@ -80,6 +80,38 @@ def test_fast_plan_pairs_runs_of_haplotypes():
             assert (s["cover"] == 1).all()
             for kh, lanes, vl, ntasks in s["classes"]:
                 assert lanes in (8, 16, 32) and 1 <= kh <= 16 and vl == 2 and ntasks > 0
+
+
+def test_fp64_first_reads_are_planned_once_and_only_when_predicted():
+    # PlanOptions::spec: reads the k-mer predictor expects to fail the FP32 pass against their whole batch get FP64-first
+    # tasks (heads of the rescue lists) instead of a place in an FP32 class; every pair is still produced exactly once
+    for fb in (synth.c1_small(0.03), synth.c2_large(60000), synth.c4_stress(800), synth.c5_skewed(6000), synth.edge_cases()):
+        s = phmm.plan_summary(fb, fast=True, fp64_first=True)
+        assert (s["cover"] == 1).all() and s["pairs"] == fb.n_pairs and s["cells"] == fb.n_cells
+        _, pred = phmm.batch_costs(fb, fast=True, predicted=True)
+        sure = (pred & 2) != 0
+        nh_of_read = np.repeat(fb.batch_num_haps, fb.batch_num_reads)
+        # (small calls are planned for latency and keep every read in the FP32 classes)
+        assert s["fp64_first_pairs"] in (0, int(nh_of_read[sure & (fb.read_len <= 255)].sum()))
+        assert (s["fp64_first_pairs"] > 0) == (s["fp64_first_cells"] > 0)
+        assert sum(c for c, _ in s["class_cells"]) + s["fp64_first_cells"] == fb.n_cells
+        assert not ((pred & 2) != 0)[(pred & 1) == 0].any()          # "all pairs, by a factor of ten" implies "most pairs"
+    assert phmm.plan_summary(synth.c2_large(60000), fast=True, fp64_first=True)["fp64_first_pairs"] > 0
+    clean = synth.generic(5, 200, (40, 40), (8, 8), (100, 150), (150, 300), foreign_frac=0.0)
+    assert phmm.plan_summary(clean, fast=True, fp64_first=True)["fp64_first_pairs"] == 0
+    dirty = synth.generic(5, 200, (40, 40), (8, 8), (100, 150), (150, 300), foreign_frac=0.9)
+    assert phmm.plan_summary(dirty, fast=True, fp64_first=True)["fp64_first_pairs"] > 0.5 * dirty.n_pairs
+    # the per-call rule (plan_spec): only where a read is enough device work to pay for its prediction, and only when a
+    # sample of the reads has such reads at all
+    many_haps = dict(reads_rng=(20, 40), haps_rng=(40, 64), rlen_rng=(100, 250), hlen_rng=(150, 473))
+    assert phmm.plan_summary(synth.generic(6, 40, foreign_frac=0.2, **many_haps), fast=True, fp64_first="auto")["fp64_first_pairs"] > 0
+    short_reads = dict(many_haps, rlen_rng=(60, 120))          # none of these hangs over its haplotype: nothing fails the FP32 pass
+    assert phmm.plan_summary(synth.generic(6, 60, foreign_frac=0.0, **short_reads), fast=True, fp64_first="auto")["fp64_first_pairs"] == 0
+    assert phmm.plan_summary(dirty, fast=True, fp64_first="auto")["fp64_first_pairs"] == 0       # 8 short haplotypes per batch
+    assert phmm.plan_summary(dirty, fast=False, fp64_first="auto")["fp64_first_pairs"] == 0
+    # a one-wave call (one region) keeps its one class: no FP64-first tasks there
+    assert phmm.plan_summary(synth.generic(5, 1, (20, 20), (6, 6), (100, 150), (150, 300), foreign_frac=0.9),
+                             fast=True, fp64_first=True)["fp64_first_pairs"] == 0
 
 
 def test_one_wave_calls_are_planned_with_one_class():
