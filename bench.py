@@ -479,8 +479,9 @@ def tile_fill(fb, fast):
     """cells / tile cells of rank 0's plan: the share of the FP32 kernels' row steps that are real read rows (a read
     of R bases occupies kh x lanes rows of its class's register tile; separator columns count as tile cells too)."""
     from genomicsbench_palisade_b200 import phmm
-    p = phmm.plan_summary(fb, cover=False, fast=fast)
-    return {"real_over_tile": p["cells"] / max(1, p["tile_cells"]),
+    # planned as the library plans it (FP64-first reads, where its per-call rule has them, are in no FP32 tile)
+    p = phmm.plan_summary(fb, cover=False, fast=fast, fp64_first="auto" if fast else False)
+    return {"real_over_tile": (p["cells"] - p["fp64_first_cells"]) / max(1, p["tile_cells"]),
             "classes": [{"kh": k[0], "lanes": k[1], "real_over_tile": round(c / max(1, t), 4)}
                         for k, (c, t) in zip(p["classes"], p["class_cells"])]}
 

@@ -200,6 +200,7 @@ bool spec_enabled()
 int plan_spec(const phmm_flat_batches &fb, const PlanOptions &opt)
 {
     if (opt.spec >= 0) return opt.spec;
+    if (!spec_enabled()) return 0;
     if (!opt.hp || opt.precision != 0 || opt.latency == 1 || opt.force_kh > 0 || fb.n_reads <= 0 || fb.n_batches <= 0) return 0;
     if (!fb.batch_num_reads || !fb.batch_num_haps || !fb.read_len || !fb.hap_len || !fb.read_off || !fb.hap_off) return 0;
     double cells = 0;

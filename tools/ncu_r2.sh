@@ -27,7 +27,7 @@ dur_unit = {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "nsecond": 1e-6, "msecond":
 D = sum(float(r[du].replace(",", "")) for r in rows[2:]) * dur_unit
 json.dump({"phmm": {"kernel": "phmm_forward_hp_kernel", "launches": len(rows) - 2, "dram_read_bytes": R, "dram_write_bytes": W,
                     "traffic_bytes_per_step": R + W, "sum_duration_ms": D,
-                    "build": "round 2 final build (length-paired runs, list_class / resc_force in the kernel parameters; FP32 cell update unchanged since round 1), captured " + time.strftime("%Y-%m-%d"),
+                    "build": "round 2 final build (length-paired runs, FP64-first reads; FP32 cell update unchanged since round 1), captured " + time.strftime("%Y-%m-%d"),
                     "source": "ncu --set full --clock-control none -k phmm_forward_hp_kernel -c 12, bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --configs none; profiles/r2_phmm_ncu_full_metrics.txt"}},
           open(out + "/r2_dram_traffic.json", "w"), indent=1)
 print(open(out + "/r2_dram_traffic.json").read())
