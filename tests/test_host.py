@@ -114,6 +114,25 @@ def test_fp64_first_reads_are_planned_once_and_only_when_predicted():
                              fast=True, fp64_first=True)["fp64_first_pairs"] == 0
 
 
+def test_random_shapes_every_pair_planned_exactly_once():
+    # property: whatever the batch shapes, lengths and share of unrelated reads, and whichever plan (bit-exact classes,
+    # haplotype-pair classes, FP64-first reads forced on or by the library's rule, short runs), every pair is produced once
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=80, deadline=None, derandomize=True)
+    @given(seed=st.integers(0, 10_000), nb=st.integers(1, 12), rmax=st.integers(1, 40), hmax=st.integers(1, 30),
+           rlen=st.integers(1, 520), hlen=st.integers(1, 900), ff=st.sampled_from([0.0, 0.3, 1.0]),
+           mode=st.sampled_from([(False, False, 0), (True, False, 0), (True, True, 0), (True, "auto", 0), (True, True, 300)]))
+    def check(seed, nb, rmax, hmax, rlen, hlen, ff, mode):
+        fb = synth.generic(seed, nb, (1, rmax), (1, hmax), (1, rlen), (max(1, hlen // 3), hlen), foreign_frac=ff)
+        fast, spec, seg = mode
+        s = phmm.plan_summary(fb, fast=fast, fp64_first=spec, seg_cols=seg)
+        assert s["pairs"] == fb.n_pairs and s["cells"] == fb.n_cells and (s["cover"] == 1).all()
+        assert sum(c for c, _ in s["class_cells"]) + s["fp64_first_cells"] == fb.n_cells or s["n_classes"] > 16
+
+    check()
+
+
 def test_one_wave_calls_are_planned_with_one_class():
     # a call whose tasks fit the device in one wave (one active region): every read in the 32-lane class of the
     # longest read -- one launch per phase instead of one per class (phmm_plan.cpp: plan_one_class)
