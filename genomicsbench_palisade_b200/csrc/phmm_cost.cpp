@@ -246,7 +246,7 @@ int plan_spec(const phmm_flat_batches &fb, const PlanOptions &opt)
 }
 
 int batch_costs(const phmm_flat_batches &fb, int fast, int precision, const CostModel &m, int64_t *cost,
-                uint8_t *read_rescued)
+                uint8_t *read_rescued, int spec_plan)
 {
     if (fb.n_batches < 0 || (fb.n_batches && (!fb.batch_num_reads || !fb.batch_num_haps || !cost))) return PHMM_ERR_ARG;
     static const LogTables lt;
@@ -256,7 +256,17 @@ int batch_costs(const phmm_flat_batches &fb, int fast, int precision, const Cost
     opt.precision = precision;
     opt.hp = fast ? 1 : 0;
     opt.latency = 0;
-    const bool spec = fast && precision == 0 && spec_enabled();
+    // whether reads named "sure" cost no FP32 pass: as the library would plan this very input (the scheduler hands the
+    // whole workload over), unless the caller knows (the planner, which asks per slice of a chunk)
+    bool spec = fast && precision == 0 && spec_enabled();
+    if (spec && spec_plan < 0) {
+        PlanOptions po;
+        po.precision = 0; po.hp = 1; po.spec = -1;
+        po.latency = plan_latency(fb, po);
+        spec = plan_spec(fb, po) > 0;
+    } else if (spec) {
+        spec = spec_plan > 0;
+    }
     double w_of_len[512];
     for (double &v : w_of_len) v = -1.0;
     // tile weight of a read: device time per haplotype column, in units of one FP32 row step of the fast kernels

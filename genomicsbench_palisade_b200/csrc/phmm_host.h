@@ -106,7 +106,7 @@ CostModel default_cost_model();
 // cost[b]: predicted time of batch b (arbitrary unit); read_rescued (may be NULL): 1 where the predictor expects
 // most pairs of the read to be re-run in FP64.
 int batch_costs(const phmm_flat_batches &fb, int fast, int precision, const CostModel &m, int64_t *cost,
-                uint8_t *read_rescued);
+                uint8_t *read_rescued, int spec_plan = -1);
 // FP64-first planning on (default) unless PHMM_SPEC64=0
 bool spec_enabled();
 int plan_spec(const phmm_flat_batches &fb, const PlanOptions &opt);      // opt.latency resolved; once per call

@@ -310,7 +310,7 @@ int build_plan(const phmm_flat_batches &fb, const PlanOptions &opt_in, Plan *pla
             v.n_haps = cut_h[j + 1] - cut_h[j];
             v.hap_len = fb.hap_len + cut_h[j];
             v.hap_off = fb.hap_off + cut_h[j];
-            rcs[j] = batch_costs(v, 1, 0, default_cost_model(), cost_unused.data() + cut_b[j], pred.data() + cut_r[j]);
+            rcs[j] = batch_costs(v, 1, 0, default_cost_model(), cost_unused.data() + cut_b[j], pred.data() + cut_r[j], 1);
         };
         std::vector<std::thread> helpers;
         for (size_t j = 1; j + 1 < cut_b.size(); ++j) helpers.emplace_back(slice, j);
