@@ -960,20 +960,21 @@ static int wl_finish(phmm_ctx *ctx, phmm_workload *w, StreamSet &ss, phmm_stats 
     int64_t nres = (int64_t)counts[INTS_RESC_PAIRS - INTS_RESC] + spec_counts[MAX_KH_SCALAR + 1];
     for (int k = 0; k <= MAX_KH_SCALAR; ++k) { nguard += counts[16 + k]; n64 += counts[32 + k]; nband += spec_counts[k]; }
     w->last_spec_direct = spec_counts[MAX_KH_SCALAR + 2];
+    if (n64 > 0) {
+        // fast FP64 kernels met non-finite sums (exotic gap-continuation penalties): bit-exact re-run
+        int rc = wl_launch(ctx, w, ss, nullptr, counts + 32);
+        if (rc != PHMM_OK) return rc;
+        CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
+    }
     if (nband > 0) {
         // FP64-first pairs whose rescaled sum fell inside the band around MIN_ACCEPTED: the bit-exact FP32 kernel decides
+        // (after the re-run above: a non-finite FP64-first sum is in both lists, and the FP32 verdict has the last word)
         int rc = wl_launch(ctx, w, ss, nullptr, nullptr, spec_counts);
         if (rc != PHMM_OK) return rc;
         int32_t decided = 0;
         CUDA_TRY(ctx, cudaMemcpyAsync(&decided, w->d_ints + INTS_RESC_PAIRS, sizeof decided, cudaMemcpyDeviceToHost, ss.main));
         CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
         nres += decided - counts[INTS_RESC_PAIRS - INTS_RESC];
-    }
-    if (n64 > 0) {
-        // fast FP64 kernels met non-finite sums (exotic gap-continuation penalties): bit-exact re-run
-        int rc = wl_launch(ctx, w, ss, nullptr, counts + 32);
-        if (rc != PHMM_OK) return rc;
-        CUDA_TRY(ctx, cudaStreamSynchronize(ss.main));
     }
     w->last_rescued = nres;
     w->last_guard = nguard;

@@ -269,7 +269,8 @@ __device__ __forceinline__ void emit_result(const KernelParams<double> &P, doubl
             const int ci = list_class(P, rslen);
             const int k = atomicAdd(&P.spec_count[ci], 1);
             P.spec_list[P.spec_off[ci] + k] = nt;
-            if (!(res <= 1.7976931348623157e+308)) { P.rescued[oidx] = 1; P.out[oidx] = res; return; }
+            // (a non-finite sum of the fast FP64 kernel also takes the branch below to the bit-exact FP64 re-run, which
+            // wl_finish launches before the FP32 decision pass)
         } else {
             atomicAdd(P.spec_count + MAX_KH_SCALAR + 1, 1);
         }
